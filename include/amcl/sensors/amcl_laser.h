@@ -1,0 +1,2 @@
+/* Forwarder: "amcl/sensors/amcl_laser.h" resolves to the combined C++ ABI header. */
+#include "../../amcl_b200/amcl_sensors.hpp"
