@@ -1,0 +1,124 @@
+/*
+ * amcl_b200.h -- everything libamcl_b200.so exports, in one place.
+ *
+ * Part 1 is the drop-in boundary: the reference's own C API, re-declared in
+ * amcl_b200/amcl_abi.h with the reference file:line each entry point replaces
+ * (pf.h:147-203, map.h:88-111, pf_vector.h, pf_pdf.h, pf_kdtree.h, eig3.h), and
+ * the C++ classes in amcl_b200/amcl_sensors.hpp (amcl_sensor.h, amcl_odom.h,
+ * amcl_laser.h).  amcl_node links against those unchanged.
+ *
+ * Part 2 (amcl_c_*) is a plain-C facade over the C++ classes for FFI callers
+ * (ctypes, cgo, JNI ...) that cannot construct C++ objects.  Each function
+ * forwards to exactly one reference method; see navigation_b200/csrc/class_capi.cpp.
+ *
+ * Part 3 (amclb200_*) has no counterpart in the reference.  It exposes what a
+ * host-only API cannot express: where the particles live (HBM), when the host
+ * mirror of pf_sample_set_t::samples is refreshed, which random stream is used,
+ * and integer results (source indices, labels) that the reference only holds
+ * implicitly.  Nothing in Part 3 has to be called by a drop-in user.
+ *
+ * All pointers are HOST pointers unless a name says "device".  No function
+ * here takes or returns a torch / C++ library type.
+ */
+#ifndef AMCL_B200_H
+#define AMCL_B200_H
+
+#include <stdint.h>
+#include "amcl_b200/amcl_abi.h"   /* Part 1 (C half) */
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------------------------------------------------------- Part 2 -- */
+/* maps: what AmclNode::convertMap builds (amcl_node.cpp:987-1012) */
+map_t *amcl_c_map_from_occupancy(const signed char *occ, int size_x, int size_y,
+                                 double scale, double origin_x, double origin_y);
+void amcl_c_map_get_occ_dist(map_t *map, double *out);
+void amcl_c_map_set_occ_dist(map_t *map, const double *in, double max_occ_dist);
+/* AmclNode::uniformPoseGenerator + its free-space index (amcl_node.cpp:901-908,1050-1060) */
+int amcl_c_freespace_build(map_t *map);
+pf_vector_t amcl_c_uniform_pose(void *map);
+pf_init_model_fn_t amcl_c_uniform_pose_fn(void);
+/* AMCLOdom (amcl_odom.h:57-93) */
+void *amcl_c_odom_new(void);
+void amcl_c_odom_delete(void *odom);
+void amcl_c_odom_set_model(void *odom, int type, double a1, double a2, double a3, double a4, double a5);
+int amcl_c_odom_update_action(void *odom, pf_t *pf, const double pose[3], const double delta[3]);
+/* AMCLLaser (amcl_laser.h:59-151) */
+void *amcl_c_laser_new(int max_beams, map_t *map);
+void amcl_c_laser_delete(void *laser);
+void *amcl_c_laser_clone(void *laser);
+void amcl_c_laser_set_pose(void *laser, double x, double y, double a);
+void amcl_c_laser_set_model_beam(void *laser, double z_hit, double z_short, double z_max,
+                                 double z_rand, double sigma_hit, double lambda_short,
+                                 double chi_outlier);
+void amcl_c_laser_set_model_lf(void *laser, double z_hit, double z_rand, double sigma_hit,
+                               double max_occ_dist);
+void amcl_c_laser_set_model_lfp(void *laser, double z_hit, double z_rand, double sigma_hit,
+                                double max_occ_dist, int do_beamskip, double beam_skip_distance,
+                                double beam_skip_threshold, double beam_skip_error_threshold);
+int amcl_c_laser_update_sensor(void *laser, pf_t *pf, const double *ranges_rb, int range_count,
+                               double range_max);
+pf_sample_set_t *amcl_c_pf_current_set(pf_t *pf);
+int amcl_c_sizeof_pf(void);
+int amcl_c_sizeof_laser(void);
+int amcl_c_sizeof_odom(void);
+
+/* ---------------------------------------------------------------- Part 3 -- */
+
+/* "amcl_b200 <major>.<minor> sm_100a" */
+const char *amclb200_version(void);
+
+/* CUDA stream (a cudaStream_t passed as void*) all later launches go to.
+ * Default: the legacy default stream. */
+void amclb200_set_stream(void *cuda_stream);
+
+/* Random streams.  mode 0 = Philox4x32-10 on the device, keyed by `seed`
+ * (production default).  mode 1 = libc drand48() consumed on the host in the
+ * reference's exact order (parity with the reference for a given srand48). */
+void amclb200_set_rng(int mode, uint64_t seed);
+
+/* Host mirror policy for pf_sample_set_t::samples.  eager = 1 (default): every
+ * pf_update_* / UpdateAction / UpdateSensor call ends with a device-to-host
+ * copy of the current set, so callers that read samples[] directly
+ * (amcl_node.cpp:1342-1361) keep working.  eager = 0: the mirror is refreshed
+ * only by amclb200_pf_pull_samples. */
+void amclb200_set_mirror(pf_t *pf, int eager);
+void amclb200_pf_pull_samples(pf_t *pf);   /* device -> samples[] of the current set */
+void amclb200_pf_push_samples(pf_t *pf);   /* samples[] (+ sample_count) -> device */
+
+/* Device address of set `set_index`'s particle array: max_samples records of
+ * 32 bytes (x, y, theta, weight as fp64), the layout of pf_sample_t. */
+void *amclb200_pf_device_samples(pf_t *pf, int set_index);
+
+/* Re-encode the distances currently held in map->cells[].occ_dist (and
+ * map->max_occ_dist) into the device distance map, e.g. to evaluate the laser
+ * models on the reference wavefront's output.  Aborts on values that are not
+ * sqrt(integer)*scale. */
+void amclb200_map_push_distances(map_t *map);
+
+/* Source index of every sample of the current set as chosen by the last
+ * pf_update_resample (-1 = injected random pose); returns the count written. */
+int amclb200_pf_resample_sources(pf_t *pf, int *out, int capacity);
+
+/* Cluster label of every sample of the current set (this library's canonical
+ * numbering: clusters in order of first appearance); returns the count. */
+int amclb200_pf_cluster_labels(pf_t *pf, int *out, int capacity);
+
+/* The sequential-order cumulative weight table pf_update_resample searches
+ * (pf.c:399-402), recomputed for the current set: n+1 doubles. */
+int amclb200_pf_cumulative_table(pf_t *pf, double *out, int capacity);
+
+/* Device milliseconds (CUDA events) of the last action / sensor / resample call. */
+void amclb200_pf_last_timings(pf_t *pf, float out_ms[3]);
+
+/* Batched map_calc_range on the device: n rays (ox, oy, oa) -> ranges. */
+void amclb200_map_calc_ranges(map_t *map, const double *rays_xya, int n, double max_range,
+                              double *out_ranges);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* AMCL_B200_H */

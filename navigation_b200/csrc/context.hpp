@@ -1,0 +1,194 @@
+// context.hpp -- device-side state behind the reference's host structs.
+//
+// The reference structs (map_t, pf_t, AMCLLaser) cannot grow (they are ABI,
+// SURVEY.md 8b), so everything that lives in HBM hangs off two registries:
+//   MapCtx  keyed by map_t*   -- occupancy bytes, distance-code map, ray bitmap
+//   PfCtx   keyed by pf_t*    -- the two particle arrays and all resampling
+//                                scratch (also reachable through
+//                                pf_t::limit_cache, which only this library
+//                                interprets)
+#pragma once
+
+#include <stdint.h>
+#include <vector>
+
+#include "amcl/map/map.h"
+#include "amcl/pf/pf.h"
+#include "common.cuh"
+
+namespace amclb200
+{
+
+// ---- library-wide settings ----------------------------------------------------
+
+enum RngMode
+{
+  RNG_PHILOX = 0,   // production: counter-based streams generated on device
+  RNG_DRAND48 = 1   // parity: uniforms drawn from libc drand48() on the host in
+                    // the reference's exact order, then shipped to the device
+};
+
+struct Globals
+{
+  cudaStream_t stream = 0;     // all launches; 0 = legacy default stream
+  RngMode rng = RNG_PHILOX;
+  uint64_t philox_seed = 0x243F6A8885A308D3ull;
+  int sm_count = 0;
+  int device = -1;
+  bool exact_cumsum_parallel = false;  // tile-classified exact scan vs 1-thread walk
+};
+Globals &globals();
+void ensure_device();           // fills sm_count/device once; aborts without a GPU
+
+// ---- distance-code map ----------------------------------------------------------
+//
+// Every value occ_dist can take is sqrt(d2)*scale with integer d2 <= R^2, or
+// max_occ_dist (map_cspace.cpp:49,102-105,148).  The device keeps a uint16
+// CODE per cell: d2 itself (0..R^2), R^2+1 for "farther than R".  Cells are
+// stored in 4x4 blocks of 16 codes = 32 B = one L2 sector, blocks row-major,
+// so neighbouring beam end points (in any direction) share sectors.
+constexpr int kTile = 4;
+
+struct MapCtx
+{
+  map_t *host = nullptr;
+  int sx = 0, sy = 0;
+  int tiles_x = 0, tiles_y = 0;
+  double scale = 0, origin_x = 0, origin_y = 0;
+  int R = 0;                      // cell radius of the current distance map
+  double max_occ_dist = 0;
+  bool occ_uploaded = false;
+  bool dist_valid = false;
+  uint64_t generation = 0;        // bumps whenever codes / R / scale change
+
+  int8_t *d_occ = nullptr;        // [sy][sx] occupancy states
+  uint16_t *d_code = nullptr;     // tiled distance codes
+  uint64_t *d_blocked = nullptr;  // 8x8-cell bit tiles: bit set = ray stops here
+  int btiles_x = 0, btiles_y = 0;
+  uint8_t *d_rowdist = nullptr;   // EDT pass-1 scratch (uint16 when R > 254)
+  std::vector<double> dist_of_code;  // host: code -> metres (incl. sentinel)
+
+  int code_far() const { return R * R + 1; }
+};
+
+MapCtx *map_ctx(map_t *map, bool create);
+void map_ctx_release(map_t *map);
+void map_upload_occupancy(MapCtx *m);            // host cells -> d_occ, d_blocked
+void map_build_distance_codes(MapCtx *m, double max_occ_dist);  // exact EDT
+void map_codes_to_host_cells(MapCtx *m);         // fills cells[].occ_dist
+void map_codes_from_host_cells(MapCtx *m);       // encodes cells[].occ_dist
+
+// ---- particle filter -------------------------------------------------------------
+
+struct HashSlot
+{
+  unsigned long long key;   // packed bin key, kEmptyKey when free
+  unsigned int first;       // smallest sample index that landed here
+  unsigned int aux;         // union-find parent, later the cluster id
+};
+constexpr unsigned long long kEmptyKey = ~0ull;
+
+struct PfCtx
+{
+  pf_t *host = nullptr;
+  int max_samples = 0;
+  Particle *d_set[2] = {nullptr, nullptr};
+  bool mirror_eager = true;       // D2H the sample array after every update
+  bool host_fresh[2] = {false, false};
+
+  // resampling scratch
+  double *d_cum = nullptr;        // max+1 cumulative table
+  double *d_draws = nullptr;      // 2*max uniforms (u_test, r) or 6*max (motion)
+  int *d_src = nullptr;           // source index per output sample
+  unsigned long long *d_keys = nullptr;
+  unsigned int *d_slot = nullptr; // hash slot per sample
+  unsigned int *d_flag = nullptr; // scan input
+  unsigned int *d_scan = nullptr; // scan output [max] + per-slot scratch [hash_cap]
+  unsigned int *d_scan_tiles = nullptr;  // per-tile sums of the u32 scan
+  int scan_tiles_cap = 0;
+  int *d_label = nullptr;         // cluster label per sample (canonical numbering)
+  HashSlot *d_hash = nullptr;
+  unsigned int hash_cap = 0;      // power of two
+  double *d_cluster_acc = nullptr;  // [cluster][10]
+  int cluster_acc_cap = 0;
+  double *d_partials = nullptr;   // per-block partial sums (several lanes)
+  int partials_cap = 0;
+  double *d_scalars = nullptr;    // small device scratch (64 doubles)
+  double *h_scalars = nullptr;    // pinned mirror of d_scalars
+  int *d_ints = nullptr;          // small device scratch (64 ints + beam counts)
+  int *h_ints = nullptr;          // pinned
+  int ints_cap = 0;
+  // exact cumulative-sum scratch
+  double *d_tile_sum = nullptr;
+  double *d_tile_carry = nullptr;
+  unsigned long long *d_tile_fn = nullptr;  // 2 words per tile
+  int *d_tile_class = nullptr;
+  int tile_cap = 0;
+
+  // laser staging (beam table + LUT), sized on demand
+  double *d_scan_tab = nullptr;
+  int scan_tab_cap = 0;
+  double *d_lut = nullptr;
+  int lut_cap = 0;
+
+  uint64_t step = 0;              // counter feeding the Philox key
+  unsigned long long draws_used = 0;
+
+  // last-call timings (ms, CUDA events), for bench/diagnostics
+  float ms_action = 0, ms_sensor = 0, ms_resample = 0;
+};
+
+PfCtx *pf_ctx(pf_t *pf);                       // aborts if unknown
+PfCtx *pf_ctx_of_set(pf_sample_set_t *set, int *which);
+PfCtx *pf_ctx_create(pf_t *pf);
+void pf_ctx_release(pf_t *pf);
+void pf_pull(PfCtx *c, int which);             // device -> host mirror
+void pf_push(PfCtx *c, int which);             // host mirror -> device
+void pf_after_update(PfCtx *c, int which);     // honours mirror_eager
+
+// ---- stage launchers (device pointers, run on globals().stream) -----------------
+
+struct LaserScanHost
+{
+  // beams that survive the reference's skip rules, in scan order
+  std::vector<double> a, b;      // r*cos(bearing)/scale, r*sin(bearing)/scale
+  std::vector<double> range;     // r (beam model)
+  std::vector<double> cb, sb;    // cos/sin(bearing) (beam model)
+  std::vector<int> beam_ind;     // position in the reference's beam_ind numbering
+};
+
+// likelihood_field (model 1) / likelihood_field_prob (model 2); returns the
+// unnormalised total weight (pf_sensor_model_fn_t contract).
+double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
+                            const double laser_pose[3], const LaserScanHost &scan,
+                            const std::vector<double> &lut, const int *mask_or_null,
+                            int n_beam_slots, int *agree_counts_or_null,
+                            const std::vector<unsigned char> *agree_lut);
+double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3],
+                      const LaserScanHost &scan, double range_max, const double zp[6]);
+// pf.c:282-316 on device; returns n_effective, updates pf w_slow/w_fast
+void run_sensor_normalise(PfCtx *c, int which, double total);
+void run_calc_ranges(MapCtx *m, const double *rays_xya, int n, double max_range, double *out);
+
+void run_motion(PfCtx *c, int which, int model, const double consts[8],
+                const double *host_draws_or_null);
+void run_resample(PfCtx *c);
+void run_cluster_stats(PfCtx *c, int which, bool histogram_ready);
+int run_update_converged(PfCtx *c, int which);
+void run_cep_stats(PfCtx *c, int which, double out[4]);   // mn, mx, my, mrr
+void run_copy_set(PfCtx *c, int from, int to);
+void run_philox_gaussian_init(PfCtx *c, int which, const double mean[3],
+                              const double cr[9], const double cd[3]);
+
+// exact sequential-order cumulative table (pf.c:399-402) of the weights of a set
+void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum);
+
+struct StageTimer
+{
+  cudaEvent_t a, b;
+  float *out;
+  explicit StageTimer(float *dst);
+  ~StageTimer();
+};
+
+}  // namespace amclb200

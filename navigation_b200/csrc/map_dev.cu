@@ -1,0 +1,468 @@
+// map_dev.cu -- occupancy grid on the device: exact bounded Euclidean distance
+// transform (stands in for the priority-queue wavefront of
+// /root/reference/amcl/src/amcl/map/map_cspace.cpp:120-176), the ray bitmap for
+// the beam model, and the map_* entry points of map.h:88-111.
+//
+// Distance semantics.  The reference's wavefront is NOT an exact transform: a
+// cell keeps whatever source reached it first (map_cspace.cpp:95-116).
+// north_star asks for an exact EDT, so this file computes, per cell,
+//     d2 = min over occupied cells of (di^2 + dj^2)
+// and stores d2 (or "far" when d2 > R^2, R = (int)(max_occ_dist/scale),
+// map_cspace.cpp:42,102).  occ_dist on the host is then sqrt(d2)*scale with one
+// IEEE sqrt and one multiply, the reference's own arithmetic (:49,:105), so it
+// equals the reference bit-for-bit wherever the reference itself is exact, and
+// is never larger.  See DESIGN.md "C1".
+#include <math.h>
+#include <string.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "context.hpp"
+
+namespace amclb200
+{
+
+// ------------------------------------------------------------------ globals --
+
+Globals &globals()
+{
+  static Globals g;
+  return g;
+}
+
+void ensure_device()
+{
+  Globals &g = globals();
+  if (g.device >= 0) return;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+    AMCL_FATAL("no CUDA device: libamcl_b200 has no CPU path (%s)",
+               e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  int dev = 0;
+  AMCL_CUDA(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  AMCL_CUDA(cudaGetDeviceProperties(&prop, dev));
+  g.device = dev;
+  g.sm_count = prop.multiProcessorCount;
+}
+
+StageTimer::StageTimer(float *dst) : out(dst)
+{
+  AMCL_CUDA(cudaEventCreate(&a));
+  AMCL_CUDA(cudaEventCreate(&b));
+  AMCL_CUDA(cudaEventRecord(a, globals().stream));
+}
+
+StageTimer::~StageTimer()
+{
+  AMCL_CUDA(cudaEventRecord(b, globals().stream));
+  AMCL_CUDA(cudaEventSynchronize(b));
+  AMCL_CUDA(cudaEventElapsedTime(out, a, b));
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+}
+
+// ----------------------------------------------------------------- registry --
+
+static std::unordered_map<map_t *, MapCtx *> &map_registry()
+{
+  static std::unordered_map<map_t *, MapCtx *> r;
+  return r;
+}
+
+MapCtx *map_ctx(map_t *map, bool create)
+{
+  auto &r = map_registry();
+  auto it = r.find(map);
+  if (it != r.end())
+  {
+    MapCtx *m = it->second;
+    // the caller may have re-filled the struct (reconfigure path)
+    if (m->sx != map->size_x || m->sy != map->size_y)
+    {
+      map_ctx_release(map);
+      return map_ctx(map, create);
+    }
+    m->scale = map->scale;
+    m->origin_x = map->origin_x;
+    m->origin_y = map->origin_y;
+    return m;
+  }
+  if (!create) return nullptr;
+  ensure_device();
+  if (map->size_x <= 0 || map->size_y <= 0 || map->cells == nullptr)
+    AMCL_FATAL("map_t has no cells (size %d x %d)", map->size_x, map->size_y);
+  MapCtx *m = new MapCtx();
+  m->host = map;
+  m->sx = map->size_x;
+  m->sy = map->size_y;
+  m->scale = map->scale;
+  m->origin_x = map->origin_x;
+  m->origin_y = map->origin_y;
+  m->tiles_x = (m->sx + kTile - 1) / kTile;
+  m->tiles_y = (m->sy + kTile - 1) / kTile;
+  m->btiles_x = (m->sx + 7) / 8;
+  m->btiles_y = (m->sy + 7) / 8;
+  size_t cells = (size_t)m->sx * m->sy;
+  AMCL_CUDA(cudaMalloc(&m->d_occ, cells));
+  AMCL_CUDA(cudaMalloc(&m->d_code, (size_t)m->tiles_x * m->tiles_y * 16 * sizeof(uint16_t)));
+  AMCL_CUDA(cudaMalloc(&m->d_blocked, (size_t)m->btiles_x * m->btiles_y * sizeof(uint64_t)));
+  AMCL_CUDA(cudaMalloc(&m->d_rowdist, cells * sizeof(uint16_t)));
+  r[map] = m;
+  return m;
+}
+
+void map_ctx_release(map_t *map)
+{
+  auto &r = map_registry();
+  auto it = r.find(map);
+  if (it == r.end()) return;
+  MapCtx *m = it->second;
+  cudaFree(m->d_occ);
+  cudaFree(m->d_code);
+  cudaFree(m->d_blocked);
+  cudaFree(m->d_rowdist);
+  delete m;
+  r.erase(it);
+}
+
+// ------------------------------------------------------------------ kernels --
+
+// One thread per 8x8 bit tile: bit (lj*8+li) is set when a ray must stop in
+// that cell, i.e. occ_state > -1 (map_range.c:89,110).  Cells outside the map
+// inside a partial edge tile are marked blocked too.
+__global__ void build_blocked_bits(const int8_t *__restrict__ occ, int sx, int sy,
+                                   int btx, int bty, uint64_t *__restrict__ bits)
+{
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= btx * bty) return;
+  int bi = t % btx, bj = t / btx;
+  uint64_t word = 0;
+  for (int lj = 0; lj < 8; lj++)
+  {
+    int j = bj * 8 + lj;
+    for (int li = 0; li < 8; li++)
+    {
+      int i = bi * 8 + li;
+      bool blocked = true;
+      if (i < sx && j < sy) blocked = occ[(size_t)j * sx + i] > -1;
+      if (blocked) word |= 1ull << (lj * 8 + li);
+    }
+  }
+  bits[t] = word;
+}
+
+// EDT pass 1: for every cell the distance (in cells, along the row) to the
+// nearest occupied cell of the same row, capped at R+1.  One block handles a
+// row segment; the segment plus an R-cell apron sits in shared memory.
+constexpr int kRowSeg = 512;
+
+__global__ void edt_row_pass(const int8_t *__restrict__ occ, int sx, int sy, int R,
+                             uint16_t *__restrict__ rowdist)
+{
+  extern __shared__ unsigned char s_occ[];  // kRowSeg + 2R
+  const int j = blockIdx.y;
+  const int i0 = blockIdx.x * kRowSeg;
+  const int span = kRowSeg + 2 * R;
+  const int8_t *row = occ + (size_t)j * sx;
+  for (int k = threadIdx.x; k < span; k += blockDim.x)
+  {
+    int i = i0 - R + k;
+    s_occ[k] = (i >= 0 && i < sx && row[i] == 1) ? 1 : 0;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < kRowSeg; k += blockDim.x)
+  {
+    int i = i0 + k;
+    if (i >= sx) break;
+    int c = k + R;
+    int best = R + 1;
+    for (int d = 0; d <= R; d++)
+    {
+      if (s_occ[c - d] | s_occ[c + d])
+      {
+        best = d;
+        break;
+      }
+    }
+    rowdist[(size_t)j * sx + i] = (uint16_t)best;
+  }
+}
+
+// EDT pass 2: d2(i,j) = min over |dj| <= R of dj^2 + g(i, j+dj)^2, thresholded
+// at R^2.  A block owns a 32 (x) by 32 (y) cell patch; the column window
+// (32 + 2R rows) of g is staged in shared memory; results leave through shared
+// memory so that each 4x4 tile is written as one contiguous 32-byte sector.
+constexpr int kPatch = 32;
+
+__global__ void edt_col_pass(const uint16_t *__restrict__ rowdist, int sx, int sy, int R,
+                             int tiles_x, uint16_t *__restrict__ code)
+{
+  extern __shared__ uint16_t s_g[];  // (kPatch + 2R) * kPatch, then kPatch*kPatch out
+  const int i0 = blockIdx.x * kPatch, j0 = blockIdx.y * kPatch;
+  const int rows = kPatch + 2 * R;
+  const int far = R + 1;
+  for (int k = threadIdx.x; k < rows * kPatch; k += blockDim.x)
+  {
+    int lj = k / kPatch, li = k % kPatch;
+    int j = j0 - R + lj, i = i0 + li;
+    uint16_t g = (uint16_t)far;
+    if (j >= 0 && j < sy && i < sx) g = rowdist[(size_t)j * sx + i];
+    s_g[k] = g;
+  }
+  __syncthreads();
+  uint16_t *s_out = s_g + rows * kPatch;
+  const int R2 = R * R;
+  for (int k = threadIdx.x; k < kPatch * kPatch; k += blockDim.x)
+  {
+    int lj = k / kPatch, li = k % kPatch;
+    int best = R2 + 1;
+    // walk outwards from the own row; stop once dj^2 alone cannot improve
+    for (int d = 0; d <= R; d++)
+    {
+      int dd = d * d;
+      if (dd >= best) break;
+      int ga = s_g[(lj + R - d) * kPatch + li];
+      int gb = s_g[(lj + R + d) * kPatch + li];
+      int g = ga < gb ? ga : gb;
+      int v = dd + g * g;
+      if (v < best) best = v;
+    }
+    if (best > R2) best = R2 + 1;
+    // position inside the patch's 8x8 grid of 4x4 tiles
+    int tj = lj >> 2, ti = li >> 2;
+    s_out[(tj * (kPatch / kTile) + ti) * 16 + (lj & 3) * 4 + (li & 3)] = (uint16_t)best;
+  }
+  __syncthreads();
+  // 64 tiles per patch, 16 codes (32 B) each; a thread moves one 8-byte quarter
+  const int quarters = (kPatch / kTile) * (kPatch / kTile) * 4;
+  for (int q = threadIdx.x; q < quarters; q += blockDim.x)
+  {
+    int tile = q >> 2, part = q & 3;
+    int tj = tile / (kPatch / kTile), ti = tile % (kPatch / kTile);
+    int gi = (i0 >> 2) + ti, gj = (j0 >> 2) + tj;
+    if (gi * kTile >= sx || gj * kTile >= sy) continue;
+    const uint2 *src = reinterpret_cast<const uint2 *>(s_out + tile * 16 + part * 4);
+    uint2 *dst = reinterpret_cast<uint2 *>(code + ((size_t)gj * tiles_x + gi) * 16 + part * 4);
+    *dst = *src;
+  }
+}
+
+// ------------------------------------------------------------ host-side glue --
+
+void map_upload_occupancy(MapCtx *m)
+{
+  const map_t *map = m->host;
+  size_t cells = (size_t)m->sx * m->sy;
+  std::vector<int8_t> occ(cells);
+  for (size_t k = 0; k < cells; k++)
+  {
+    int s = map->cells[k].occ_state;
+    occ[k] = (int8_t)(s > 0 ? 1 : (s < 0 ? -1 : 0));
+  }
+  cudaStream_t st = globals().stream;
+  AMCL_CUDA(cudaMemcpyAsync(m->d_occ, occ.data(), cells, cudaMemcpyHostToDevice, st));
+  int nt = m->btiles_x * m->btiles_y;
+  build_blocked_bits<<<(nt + 255) / 256, 256, 0, st>>>(m->d_occ, m->sx, m->sy, m->btiles_x,
+                                                         m->btiles_y, m->d_blocked);
+  AMCL_LAUNCH_CHECK();
+  AMCL_CUDA(cudaStreamSynchronize(st));  // occ is a stack-lifetime staging buffer
+  m->occ_uploaded = true;
+}
+
+static void set_code_table(MapCtx *m, double max_occ_dist)
+{
+  // map_cspace.cpp:42 -- truncation of an fp64 quotient, e.g. 0.3/0.1 -> 2
+  int R = (int)(max_occ_dist / m->scale);
+  if (R < 0) R = 0;
+  if (R > 254)
+    AMCL_FATAL("max_occ_dist/scale = %d cells exceeds the 254-cell radius the uint16 "
+               "distance codes are sized for", R);
+  m->R = R;
+  m->max_occ_dist = max_occ_dist;
+  m->dist_of_code.assign((size_t)R * R + 2, 0.0);
+  for (int d2 = 0; d2 <= R * R; d2++)
+    m->dist_of_code[d2] = sqrt((double)d2) * m->scale;   // map_cspace.cpp:49,105
+  m->dist_of_code[(size_t)R * R + 1] = max_occ_dist;      // map_cspace.cpp:148
+}
+
+void map_build_distance_codes(MapCtx *m, double max_occ_dist)
+{
+  set_code_table(m, max_occ_dist);
+  cudaStream_t st = globals().stream;
+  const int R = m->R;
+  dim3 g1((m->sx + kRowSeg - 1) / kRowSeg, m->sy);
+  edt_row_pass<<<g1, 256, kRowSeg + 2 * R, st>>>(m->d_occ, m->sx, m->sy, R,
+                                                 (uint16_t *)m->d_rowdist);
+  AMCL_LAUNCH_CHECK();
+  dim3 g2((m->sx + kPatch - 1) / kPatch, (m->sy + kPatch - 1) / kPatch);
+  size_t smem = ((size_t)(kPatch + 2 * R) * kPatch + kPatch * kPatch) * sizeof(uint16_t);
+  if (smem > 48 * 1024)
+    AMCL_CUDA(cudaFuncSetAttribute(edt_col_pass, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)smem));
+  edt_col_pass<<<g2, 256, smem, st>>>((const uint16_t *)m->d_rowdist, m->sx, m->sy, R,
+                                      m->tiles_x, m->d_code);
+  AMCL_LAUNCH_CHECK();
+  m->dist_valid = true;
+  m->generation++;
+}
+
+void map_codes_to_host_cells(MapCtx *m)
+{
+  size_t ncodes = (size_t)m->tiles_x * m->tiles_y * 16;
+  std::vector<uint16_t> codes(ncodes);
+  AMCL_CUDA(cudaMemcpyAsync(codes.data(), m->d_code, ncodes * sizeof(uint16_t),
+                            cudaMemcpyDeviceToHost, globals().stream));
+  AMCL_CUDA(cudaStreamSynchronize(globals().stream));
+  map_t *map = m->host;
+  const double *lut = m->dist_of_code.data();
+  for (int j = 0; j < m->sy; j++)
+  {
+    const uint16_t *trow = codes.data() + (size_t)(j >> 2) * m->tiles_x * 16 + (j & 3) * 4;
+    map_cell_t *crow = map->cells + (size_t)j * m->sx;
+    for (int i = 0; i < m->sx; i++)
+      crow[i].occ_dist = lut[trow[(size_t)(i >> 2) * 16 + (i & 3)]];
+  }
+  map->max_occ_dist = m->max_occ_dist;
+}
+
+// Inverse of the above: take whatever distances the caller wrote into
+// cells[].occ_dist (e.g. the reference wavefront's output, for like-for-like
+// sensor parity) and encode them.  Every value must be one the code table can
+// express exactly; anything else is a caller error and aborts.
+void map_codes_from_host_cells(MapCtx *m)
+{
+  map_t *map = m->host;
+  set_code_table(m, map->max_occ_dist);
+  const int R2 = m->R * m->R;
+  size_t ncodes = (size_t)m->tiles_x * m->tiles_y * 16;
+  std::vector<uint16_t> codes(ncodes, (uint16_t)(R2 + 1));
+  for (int j = 0; j < m->sy; j++)
+    for (int i = 0; i < m->sx; i++)
+    {
+      double d = map->cells[(size_t)j * m->sx + i].occ_dist;
+      int code;
+      if (d == m->max_occ_dist)
+        code = R2 + 1;
+      else
+      {
+        double q = d / m->scale;
+        long d2 = lround(q * q);
+        if (d2 < 0 || d2 > R2 || m->dist_of_code[d2] != d)
+          AMCL_FATAL("occ_dist %.17g at cell (%d,%d) is not sqrt(d2)*scale for an integer "
+                     "d2 <= %d; cannot encode", d, i, j, R2);
+        code = (int)d2;
+      }
+      codes[((size_t)(j >> 2) * m->tiles_x + (i >> 2)) * 16 + (j & 3) * 4 + (i & 3)] =
+          (uint16_t)code;
+    }
+  AMCL_CUDA(cudaMemcpyAsync(m->d_code, codes.data(), ncodes * sizeof(uint16_t),
+                            cudaMemcpyHostToDevice, globals().stream));
+  AMCL_CUDA(cudaStreamSynchronize(globals().stream));
+  m->dist_valid = true;
+  m->generation++;
+}
+
+}  // namespace amclb200
+
+// ===================================================================== C API ==
+
+using namespace amclb200;
+
+extern "C" {
+
+// map.c:38-57
+map_t *map_alloc(void)
+{
+  map_t *map = (map_t *)malloc(sizeof(map_t));
+  map->origin_x = 0;
+  map->origin_y = 0;
+  map->size_x = 0;
+  map->size_y = 0;
+  map->scale = 0;
+  map->cells = (map_cell_t *)NULL;
+  map->max_occ_dist = 0;
+  return map;
+}
+
+// map.c:61-66 -- cells were malloc'd by the caller and are freed here.
+void map_free(map_t *map)
+{
+  if (!map) return;
+  map_ctx_release(map);
+  free(map->cells);
+  free(map);
+}
+
+// map.c:70-84 -- a single host-side lookup into the host mirror of the grid.
+map_cell_t *map_get_cell(map_t *map, double ox, double oy, double oa)
+{
+  (void)oa;
+  int i = MAP_GXWX(map, ox);
+  int j = MAP_GYWY(map, oy);
+  if (!MAP_VALID(map, i, j)) return NULL;
+  return map->cells + MAP_INDEX(map, i, j);
+}
+
+// map_store.c:41 loads a PGM from disk; the node never calls it (it converts a
+// ROS message itself) and file I/O is outside the path.  Exported so that
+// anything linking the symbol still links; reports failure.
+int map_load_occ(map_t *map, const char *filename, double scale, int negate)
+{
+  (void)map; (void)scale; (void)negate;
+  fprintf(stderr, "[amcl_b200] map_load_occ(%s): PGM loading is out of scope; fill map_t "
+                  "yourself as amcl_node's convertMap does\n", filename ? filename : "");
+  return -1;
+}
+
+// map_cspace.cpp:120-176.  Uploads the occupancy states, runs the exact EDT on
+// the device and writes occ_dist back into the caller's cells.
+void map_update_cspace(map_t *map, double max_occ_dist)
+{
+  MapCtx *m = map_ctx(map, true);
+  map_upload_occupancy(m);
+  map_build_distance_codes(m, max_occ_dist);
+  map_codes_to_host_cells(m);
+}
+
+// map_range.c:38-120.  A single ray is a host call in the reference API (the
+// node never issues it; the beam model's rays run in the device kernel, see
+// sensor_dev.cu).  This walks the caller's own cells with the same integer
+// line stepping so isolated queries need no device round trip.
+double map_calc_range(map_t *map, double ox, double oy, double oa, double max_range)
+{
+  int x0 = MAP_GXWX(map, ox), y0 = MAP_GYWY(map, oy);
+  int x1 = MAP_GXWX(map, ox + max_range * cos(oa));
+  int y1 = MAP_GYWY(map, oy + max_range * sin(oa));
+  const bool steep = abs(y1 - y0) > abs(x1 - x0);
+  if (steep)
+  {
+    int t = x0; x0 = y0; y0 = t;
+    t = x1; x1 = y1; y1 = t;
+  }
+  const int dx = abs(x1 - x0), dy = abs(y1 - y0);
+  const int xs = x0 < x1 ? 1 : -1, ys = y0 < y1 ? 1 : -1;
+  int x = x0, y = y0, err = 0;
+  // The reference tests the start cell, then keeps stepping until x has gone
+  // one cell PAST x1 (its loop condition is x != x1 + xstep), testing after
+  // every step.
+  for (;;)
+  {
+    int ci = steep ? y : x, cj = steep ? x : y;
+    if (!MAP_VALID(map, ci, cj) || map->cells[MAP_INDEX(map, ci, cj)].occ_state > -1)
+      return sqrt((double)((x - x0) * (x - x0) + (y - y0) * (y - y0))) * map->scale;
+    if (x == x1 + xs) break;
+    x += xs;
+    err += dy;
+    if (2 * err >= dx)
+    {
+      y += ys;
+      err -= dx;
+    }
+  }
+  return max_range;
+}
+
+}  // extern "C"

@@ -1,0 +1,1047 @@
+// resample_dev.cu -- KLD-adaptive multinomial resampling, pose histogram,
+// cluster labelling and cluster / set statistics on the device.  Stands in for
+//   pf_update_resample, copy_set, pf_resample_limit   pf.c:321-555
+//   pf_kdtree_insert / _cluster / _get_cluster         pf_kdtree.c:112-439
+//   pf_cluster_stats, pf_update_converged, cep stats   pf.c:220-251, 559-740
+// (paths under /root/reference/amcl/src/amcl/pf/).
+//
+// How the sequential reference loop becomes data-parallel without changing its
+// results:
+//  * The live sampler is MULTINOMIAL (pf.c:458-466; the low-variance code is
+//    commented out): sample m takes the source i with c[i] <= r_m < c[i+1].
+//    That is "how many of c[1..N] are <= r_m" -- a binary search per draw.
+//  * c[] must be the SEQUENTIAL fp64 running sum (pf.c:399-402) bit for bit,
+//    or draws that land within rounding of a boundary pick another index:
+//    exact_cumsum() below reproduces it exactly (see that function).
+//  * leaf_count after m insertions == number of distinct bin keys among
+//    samples 0..m: a hash insert that keeps the minimum sample index per key
+//    marks "first occurrences"; an inclusive scan of those marks is k_m.
+//  * The loop stops at the first m with (m+1) > limit(k_m) (pf.c:483): a min-
+//    reduction.  limit() is evaluated with IEEE fp64 ops and no contraction,
+//    so it returns the integers the host formula returns.
+//  * Clusters are the 26-connected components of occupied bins
+//    (pf_kdtree.c:407-438): lock-free union-find over the hash slots.  Cluster
+//    NUMBERS here are canonical -- clusters are numbered in the order their
+//    first sample appears -- because the reference's numbering is an artefact
+//    of kd-tree node allocation order (C4).  Statistics are per-cluster sums.
+#include <math.h>
+#include <float.h>
+#include <string.h>
+
+#include <vector>
+
+#include "context.hpp"
+#include "philox.cuh"
+
+namespace amclb200
+{
+
+// ------------------------------------------------------------------ bin keys --
+
+// pf_kdtree.c:116-118: key = floor(pose / size) per axis, IEEE division.
+// Packed as 21 | 21 | 22 bits with a bias so that neighbours differ by fixed
+// increments.  Poses beyond +-2^20 bins (524 km) are clamped.
+constexpr int kBiasXY = 1 << 20;
+constexpr int kBiasTh = 1 << 21;
+
+__host__ __device__ inline unsigned long long pack_key(int kx, int ky, int kt)
+{
+  kx = kx < -kBiasXY ? -kBiasXY : (kx >= kBiasXY ? kBiasXY - 1 : kx);
+  ky = ky < -kBiasXY ? -kBiasXY : (ky >= kBiasXY ? kBiasXY - 1 : ky);
+  kt = kt < -kBiasTh ? -kBiasTh : (kt >= kBiasTh ? kBiasTh - 1 : kt);
+  return ((unsigned long long)(kx + kBiasXY) << 43) | ((unsigned long long)(ky + kBiasXY) << 22) |
+         (unsigned long long)(kt + kBiasTh);
+}
+
+__device__ __forceinline__ int floor_div_to_int(double v, double size)
+{
+  const double q = floor(__ddiv_rn(v, size));
+  // (int) of an out-of-range double is what x86's cvttsd2si makes of it
+  if (!(q > -2147483649.0 && q < 2147483648.0)) return (int)0x80000000;
+  return (int)q;
+}
+
+__device__ __forceinline__ unsigned long long pose_key(const Particle &s, double sx, double sy,
+                                                       double st)
+{
+  return pack_key(floor_div_to_int(s.x, sx), floor_div_to_int(s.y, sy),
+                  floor_div_to_int(s.th, st));
+}
+
+__host__ __device__ inline unsigned int hash_key(unsigned long long k)
+{
+  k ^= k >> 33;
+  k *= 0xff51afd7ed558ccdull;
+  k ^= k >> 33;
+  k *= 0xc4ceb9fe1a85ec53ull;
+  k ^= k >> 33;
+  return (unsigned int)k;
+}
+
+// --------------------------------------------------------------- u32 scan ----
+
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 16;
+constexpr int kScanTile = kScanThreads * kScanItems;
+
+__device__ __forceinline__ unsigned int block_exclusive_scan_u32(unsigned int v, unsigned int *total,
+                                                                 unsigned int *s_warp)
+{
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  unsigned int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1)
+  {
+    unsigned int t = __shfl_up_sync(kFullMask, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) s_warp[wid] = inc;
+  __syncthreads();
+  if (wid == 0)
+  {
+    unsigned int w = lane < (int)(blockDim.x >> 5) ? s_warp[lane] : 0u;
+    unsigned int winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+      unsigned int t = __shfl_up_sync(kFullMask, winc, o);
+      if (lane >= o) winc += t;
+    }
+    s_warp[lane] = winc - w;          // exclusive warp offsets
+    if (lane == 31) s_warp[32] = winc;  // block total
+  }
+  __syncthreads();
+  *total = s_warp[32];
+  return inc - v + s_warp[wid];
+}
+
+__global__ void scan_tile_sums(const unsigned int *__restrict__ in, int n,
+                               unsigned int *__restrict__ tile_sums)
+{
+  __shared__ unsigned int s_warp[33];
+  const int base = blockIdx.x * kScanTile;
+  unsigned int v = 0;
+  for (int k = 0; k < kScanItems; k++)
+  {
+    int i = base + k * kScanThreads + threadIdx.x;
+    if (i < n) v += in[i];
+  }
+  unsigned int total;
+  block_exclusive_scan_u32(v, &total, s_warp);
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+// single block: exclusive scan of the tile sums in place; total -> *grand
+__global__ void scan_tile_offsets(unsigned int *tile_sums, int tiles, unsigned int *grand)
+{
+  __shared__ unsigned int s_warp[33];
+  __shared__ unsigned int s_carry;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int base = 0; base < tiles; base += blockDim.x)
+  {
+    int i = base + threadIdx.x;
+    unsigned int v = i < tiles ? tile_sums[i] : 0u;
+    unsigned int total;
+    unsigned int ex = block_exclusive_scan_u32(v, &total, s_warp);
+    if (i < tiles) tile_sums[i] = ex + s_carry;
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *grand = s_carry;
+}
+
+__global__ void scan_apply(const unsigned int *__restrict__ in, int n,
+                           const unsigned int *__restrict__ tile_offsets,
+                           unsigned int *__restrict__ out_inclusive)
+{
+  __shared__ unsigned int s_warp[33];
+  const int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+  unsigned int item[kScanItems];
+  unsigned int v = 0;
+#pragma unroll
+  for (int k = 0; k < kScanItems; k++)
+  {
+    int i = base + k;
+    item[k] = i < n ? in[i] : 0u;
+    v += item[k];
+  }
+  unsigned int total;
+  unsigned int run = block_exclusive_scan_u32(v, &total, s_warp) + tile_offsets[blockIdx.x];
+#pragma unroll
+  for (int k = 0; k < kScanItems; k++)
+  {
+    run += item[k];
+    int i = base + k;
+    if (i < n) out_inclusive[i] = run;
+  }
+}
+
+// inclusive scan of n flags; returns nothing, grand total lands in d_ints[slot]
+static void scan_u32(PfCtx *c, const unsigned int *in, unsigned int *out, int n, int total_slot)
+{
+  cudaStream_t st = globals().stream;
+  const int tiles = (n + kScanTile - 1) / kScanTile;
+  unsigned int *tile_sums = c->d_scan_tiles;
+  if (tiles > c->scan_tiles_cap) AMCL_FATAL("scan tile scratch too small (%d > %d)", tiles, c->scan_tiles_cap);
+  scan_tile_sums<<<tiles, kScanThreads, 0, st>>>(in, n, tile_sums);
+  AMCL_LAUNCH_CHECK();
+  scan_tile_offsets<<<1, 1024, 0, st>>>(tile_sums, tiles,
+                                        reinterpret_cast<unsigned int *>(c->d_ints + total_slot));
+  AMCL_LAUNCH_CHECK();
+  scan_apply<<<tiles, kScanThreads, 0, st>>>(in, n, tile_sums, out);
+  AMCL_LAUNCH_CHECK();
+}
+
+// ------------------------------------------------- exact cumulative table ----
+//
+// pf.c:399-402 computes c[i+1] = fl(c[i] + w[i]) one element after another.
+// Version 1 of the device path keeps that order literally: a single thread
+// performs the dependent additions while the block streams weights in and
+// sums out through shared memory.  (The tile-parallel exact form replaces it
+// for large N; see exact_cumsum_parallel.cu when present.)
+constexpr int kSeqChunk = 4096;
+
+__global__ void cumsum_sequential(const Particle *__restrict__ set, int n, double *__restrict__ c)
+{
+  __shared__ double s_w[kSeqChunk];
+  __shared__ double s_carry;
+  if (threadIdx.x == 0)
+  {
+    s_carry = 0.0;
+    c[0] = 0.0;
+  }
+  __syncthreads();
+  for (int base = 0; base < n; base += kSeqChunk)
+  {
+    const int m = min(kSeqChunk, n - base);
+    for (int k = threadIdx.x; k < m; k += blockDim.x) s_w[k] = set[base + k].w;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+      double run = s_carry;
+      for (int k = 0; k < m; k++)
+      {
+        run = __dadd_rn(run, s_w[k]);
+        s_w[k] = run;
+      }
+      s_carry = run;
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < m; k += blockDim.x) c[base + k + 1] = s_w[k];
+    __syncthreads();
+  }
+}
+
+void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum);  // cumsum_dev.cu
+
+void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum)
+{
+  if (globals().exact_cumsum_parallel && n >= 32768)
+  {
+    exact_cumsum_parallel(c, set, n, d_cum);
+    return;
+  }
+  cumsum_sequential<<<1, 256, 0, globals().stream>>>(set, n, d_cum);
+  AMCL_LAUNCH_CHECK();
+}
+
+// ------------------------------------------------------- draw + search + copy --
+
+__global__ void philox_resample_draws(double *draws, int count, uint64_t key)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= count) return;
+  PhiloxStream rng(key, (uint64_t)m);
+  draws[2 * (size_t)m] = rng.uniform();      // compared with w_diff (pf.c:430)
+  draws[2 * (size_t)m + 1] = rng.uniform();  // the multinomial draw (pf.c:460)
+}
+
+struct PickArgs
+{
+  const Particle *src;
+  int n_src;
+  const double *cum;        // n_src + 1 entries
+  const double *draws;      // (u_test, r) per candidate
+  const Particle *injected; // random poses for candidates flagged on the host, or null
+  const int *inject_slot;   // candidate -> index into injected, -1 otherwise; or null
+  Particle *dst;
+  int *src_index;
+  unsigned long long *keys;
+  int count;
+  double bin_x, bin_y, bin_t;
+};
+
+// One thread per candidate sample m: binary search of r_m in the cumulative
+// table, pose copy, bin key.  The weight is written as 1.0 (pf.c:475) and
+// rescaled once n is known.
+__global__ void pick_and_copy(const PickArgs a)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= a.count) return;
+  Particle s;
+  int from = -1;
+  if (a.inject_slot && a.inject_slot[m] >= 0)
+    s = load_particle(a.injected + a.inject_slot[m]);
+  else
+  {
+    const double r = a.draws[2 * (size_t)m + 1];
+    int lo = 0, hi = a.n_src;  // answer = #{ i in 1..n : cum[i] <= r }
+    while (lo < hi)
+    {
+      const int mid = lo + ((hi - lo) >> 1);
+      if (a.cum[mid + 1] <= r) lo = mid + 1;
+      else hi = mid;
+    }
+    if (lo >= a.n_src) lo = a.n_src - 1;  // r beyond the table's last entry
+    from = lo;
+    s = load_particle(a.src + lo);
+  }
+  s.w = 1.0;
+  store_particle(a.dst + m, s);
+  a.src_index[m] = from;
+  a.keys[m] = pose_key(s, a.bin_x, a.bin_y, a.bin_t);
+}
+
+__global__ void keys_of_set(const Particle *__restrict__ set, int n, unsigned long long *keys,
+                            double bin_x, double bin_y, double bin_t)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n) return;
+  keys[m] = pose_key(load_particle(set + m), bin_x, bin_y, bin_t);
+}
+
+// ------------------------------------------------------------ pose histogram --
+
+__global__ void hash_insert(const unsigned long long *__restrict__ keys, int n, HashSlot *table,
+                            unsigned int mask, unsigned int *slot_of)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n) return;
+  const unsigned long long key = keys[m];
+  unsigned int h = hash_key(key) & mask;
+  for (;;)
+  {
+    const unsigned long long prev = atomicCAS(&table[h].key, kEmptyKey, key);
+    if (prev == kEmptyKey || prev == key)
+    {
+      atomicMin(&table[h].first, (unsigned int)m);
+      slot_of[m] = h;
+      return;
+    }
+    h = (h + 1) & mask;
+  }
+}
+
+__global__ void mark_first(const HashSlot *__restrict__ table, const unsigned int *__restrict__ slot_of,
+                           int n, unsigned int *flag)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n) return;
+  flag[m] = table[slot_of[m]].first == (unsigned int)m ? 1u : 0u;
+}
+
+// pf.c:515-555 with IEEE ops in source order and no contraction.  The final
+// (int) conversion follows x86 (cvttsd2si): out-of-range -> INT_MIN.
+__device__ __forceinline__ int resample_limit(int k, int min_samples, int max_samples,
+                                              double pop_err, double pop_z)
+{
+  if (k < 1 || k > max_samples) return max_samples;
+  if (k == 1) return max_samples;
+  const double km1 = (double)k - 1.0;
+  const double b = __ddiv_rn(2.0, __dmul_rn(9.0, km1));
+  const double cc = __dmul_rn(__dsqrt_rn(__ddiv_rn(2.0, __dmul_rn(9.0, km1))), pop_z);
+  const double x = __dadd_rn(__dsub_rn(1.0, b), cc);
+  double v = __ddiv_rn((double)(k - 1), __dmul_rn(2.0, pop_err));
+  v = __dmul_rn(v, x);
+  v = __dmul_rn(v, x);
+  v = __dmul_rn(v, x);
+  v = ceil(v);
+  int n;
+  if (!(v > -2147483649.0 && v < 2147483648.0)) n = (int)0x80000000;
+  else n = (int)v;
+  if (n < min_samples) return min_samples;
+  if (n > max_samples) return max_samples;
+  return n;
+}
+
+// n = min over m of (m+1) with (m+1) > limit(k_m)   (pf.c:483)
+__global__ void find_kld_cut(const unsigned int *__restrict__ k_inclusive, int count,
+                             int min_samples, int max_samples, double pop_err, double pop_z,
+                             int *cut)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= count) return;
+  const int k = (int)k_inclusive[m];
+  // limit() only changes where k changes, but evaluating it everywhere keeps
+  // the kernel branch-free; min_samples gives a cheap early reject.
+  if (m + 1 <= min_samples) return;
+  if (m + 1 > resample_limit(k, min_samples, max_samples, pop_err, pop_z)) atomicMin(cut, m + 1);
+}
+
+__global__ void set_uniform_weight(Particle *set, int n, double w)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) set[i].w = w;
+}
+
+// ------------------------------------------------------------ cluster labels --
+
+// Parent pointers are read with L2 (.cg) loads: L1 is not coherent across SMs
+// and a stale "I am a root" would make the CAS in uf_union spin.
+__device__ __forceinline__ unsigned int uf_find(HashSlot *t, unsigned int x)
+{
+  unsigned int p = __ldcg(&t[x].aux);
+  while (p != x)
+  {
+    const unsigned int gp = __ldcg(&t[p].aux);
+    if (gp != p) t[x].aux = gp;  // path halving (benign race: gp is an ancestor)
+    x = p;
+    p = gp;
+  }
+  return x;
+}
+
+__device__ __forceinline__ void uf_union(HashSlot *t, unsigned int a, unsigned int b)
+{
+  for (;;)
+  {
+    a = uf_find(t, a);
+    b = uf_find(t, b);
+    if (a == b) return;
+    if (a > b) { unsigned int s = a; a = b; b = s; }
+    // hang the larger root under the smaller one
+    if (atomicCAS(&t[b].aux, b, a) == b) return;
+  }
+}
+
+// every occupied bin (first sample < n_valid) starts as its own component
+__global__ void cc_init(HashSlot *table, const unsigned int *__restrict__ slot_of,
+                        const unsigned int *__restrict__ flag, int n_valid, unsigned int *cmin)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_valid || !flag[m]) return;
+  const unsigned int s = slot_of[m];
+  table[s].aux = s;
+  cmin[s] = 0xFFFFFFFFu;
+}
+
+// pf_kdtree.c:407-438: bins are neighbours when every key component differs
+// by at most one (26-neighbourhood, heading NOT wrapped).
+__global__ void cc_link(HashSlot *table, unsigned int mask, const unsigned int *__restrict__ slot_of,
+                        const unsigned int *__restrict__ flag, int n_valid)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_valid || !flag[m]) return;
+  const unsigned int s = slot_of[m];
+  const unsigned long long key = table[s].key;
+  // only the 13 "forward" neighbours: the relation is symmetric
+  for (int q = 14; q < 27; q++)
+  {
+    const long long dx = q / 9 - 1, dy = (q % 9) / 3 - 1, dt = (q % 9) % 3 - 1;
+    const unsigned long long nk = key + (unsigned long long)(dx * (1ll << 43) + dy * (1ll << 22) + dt);
+    unsigned int h = hash_key(nk) & mask;
+    for (;;)
+    {
+      const unsigned long long kk = table[h].key;
+      if (kk == kEmptyKey) break;
+      if (kk == nk)
+      {
+        if (table[h].first < (unsigned int)n_valid) uf_union(table, s, h);
+        break;
+      }
+      h = (h + 1) & mask;
+    }
+  }
+}
+
+// root of every occupied bin; the smallest first-sample index per component
+__global__ void cc_roots(HashSlot *table, const unsigned int *__restrict__ slot_of,
+                         const unsigned int *__restrict__ flag, int n_valid, unsigned int *cmin)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_valid || !flag[m]) return;
+  const unsigned int s = slot_of[m];
+  const unsigned int r = uf_find(table, s);
+  table[s].aux = r;
+  atomicMin(&cmin[r], (unsigned int)m);
+}
+
+// a sample opens a new cluster when it is the earliest sample of its component
+__global__ void cc_mark_cluster_first(const HashSlot *__restrict__ table,
+                                      const unsigned int *__restrict__ slot_of,
+                                      const unsigned int *__restrict__ flag, int n_valid,
+                                      const unsigned int *__restrict__ cmin, unsigned int *cflag)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_valid) return;
+  unsigned int f = 0;
+  if (flag[m])
+  {
+    const unsigned int r = table[slot_of[m]].aux;   // root (set by cc_roots)
+    f = cmin[r] == (unsigned int)m ? 1u : 0u;
+  }
+  cflag[m] = f;
+}
+
+// cluster id of a component = (number of cluster-opening samples before its
+// first sample); stored over cmin[root]
+__global__ void cc_assign_ids(const HashSlot *__restrict__ table, const unsigned int *__restrict__ slot_of,
+                              const unsigned int *__restrict__ cflag,
+                              const unsigned int *__restrict__ cscan, int n_valid, unsigned int *cid)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_valid || !cflag[m]) return;
+  const unsigned int r = table[slot_of[m]].aux;
+  cid[r] = cscan[m] - 1u;
+}
+
+// ----------------------------------------------------------------- statistics --
+
+// pf.c:603-643: per sample, ten weighted sums into its cluster's accumulators
+// [count, w, w x, w y, w cos, w sin, w xx, w xy, w yx, w yy].
+__global__ void cluster_accumulate(const Particle *__restrict__ set, int n,
+                                   const HashSlot *__restrict__ table,
+                                   const unsigned int *__restrict__ slot_of,
+                                   const unsigned int *__restrict__ cid_of_root, double *acc,
+                                   int *label_out)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = i < n;
+  unsigned int label = 0xFFFFFFFFu;
+  double v[10];
+#pragma unroll
+  for (int q = 0; q < 10; q++) v[q] = 0.0;
+  if (live)
+  {
+    const Particle s = load_particle(set + i);
+    const unsigned int root = table[slot_of[i]].aux;
+    label = cid_of_root[root];
+    double sn, cs;
+    sincos(s.th, &sn, &cs);
+    v[0] = 1.0;
+    v[1] = s.w;
+    v[2] = s.w * s.x;
+    v[3] = s.w * s.y;
+    v[4] = s.w * cs;
+    v[5] = s.w * sn;
+    v[6] = s.w * s.x * s.x;
+    v[7] = s.w * s.x * s.y;
+    v[8] = s.w * s.y * s.x;
+    v[9] = s.w * s.y * s.y;
+    if (label_out) label_out[i] = (int)label;
+  }
+  // warp-uniform label (the converged case): one atomic per warp and value
+  const unsigned int first = __shfl_sync(kFullMask, label, 0);
+  const bool uniform = __all_sync(kFullMask, label == first);
+  if (uniform)
+  {
+    if (first == 0xFFFFFFFFu) return;
+#pragma unroll
+    for (int q = 0; q < 10; q++)
+    {
+      const double t = warp_sum(v[q]);
+      if ((threadIdx.x & 31) == 0) atomicAdd(&acc[(size_t)first * 10 + q], t);
+    }
+  }
+  else if (live)
+  {
+#pragma unroll
+    for (int q = 0; q < 10; q++) atomicAdd(&acc[(size_t)label * 10 + q], v[q]);
+  }
+}
+
+// sum x, sum y (pf.c:231-236) -> block partials (two lanes of the partial array)
+__global__ void sum_xy(const Particle *__restrict__ set, int n, double *px, double *py)
+{
+  __shared__ double s_red[32];
+  double ax = 0.0, ay = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+  {
+    const double2 xy = *reinterpret_cast<const double2 *>(set + i);
+    ax += xy.x;
+    ay += xy.y;
+  }
+  const double tx = block_sum(ax, s_red);
+  const double ty = block_sum(ay, s_red);
+  if (threadIdx.x == 0)
+  {
+    px[blockIdx.x] = tx;
+    py[blockIdx.x] = ty;
+  }
+}
+
+__global__ void finish_xy(const double *px, const double *py, int count, int n, double *out)
+{
+  __shared__ double s_red[32];
+  double ax = 0.0, ay = 0.0;
+  for (int k = threadIdx.x; k < count; k += blockDim.x)
+  {
+    ax += px[k];
+    ay += py[k];
+  }
+  const double tx = block_sum(ax, s_red);
+  const double ty = block_sum(ay, s_red);
+  if (threadIdx.x == 0)
+  {
+    out[0] = tx / n;   // pf.c:237-238
+    out[1] = ty / n;
+  }
+}
+
+// pf.c:240-247: any sample farther than dist_threshold from the mean on either axis
+__global__ void any_outside(const Particle *__restrict__ set, int n, const double *mean,
+                            double thr, int *flag)
+{
+  const double mx = mean[0], my = mean[1];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+  {
+    const double2 xy = *reinterpret_cast<const double2 *>(set + i);
+    if (fabs(xy.x - mx) > thr || fabs(xy.y - my) > thr)
+    {
+      *flag = 1;
+      return;
+    }
+  }
+}
+
+// pf.c:701-740 raw sums: mn, mx, my, mrr
+__global__ void cep_sums(const Particle *__restrict__ set, int n, double *partials, int stride)
+{
+  __shared__ double s_red[32];
+  double a[4] = {0, 0, 0, 0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+  {
+    const Particle s = load_particle(set + i);
+    a[0] += s.w;
+    a[1] += s.w * s.x;
+    a[2] += s.w * s.y;
+    a[3] += s.w * s.x * s.x;
+    a[3] += s.w * s.y * s.y;
+  }
+  for (int q = 0; q < 4; q++)
+  {
+    const double t = block_sum(a[q], s_red);
+    if (threadIdx.x == 0) partials[q * stride + blockIdx.x] = t;
+  }
+}
+
+__global__ void finish_multi(const double *partials, int stride, int count, int lanes, double *out)
+{
+  __shared__ double s_red[32];
+  for (int q = 0; q < lanes; q++)
+  {
+    double v = 0.0;
+    for (int k = threadIdx.x; k < count; k += blockDim.x) v += partials[q * stride + k];
+    const double t = block_sum(v, s_red);
+    if (threadIdx.x == 0) out[q] = t;
+    __syncthreads();
+  }
+}
+
+__global__ void sum_weights(const Particle *__restrict__ set, int n, double *partials)
+{
+  __shared__ double s_red[32];
+  double a = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    a += set[i].w;
+  const double t = block_sum(a, s_red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = t;
+}
+
+__global__ void copy_scaled(const Particle *__restrict__ src, Particle *dst, int n,
+                            const double *total)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Particle s = load_particle(src + i);
+  s.w = s.w / total[0];   // pf.c:353-357
+  store_particle(dst + i, s);
+}
+
+// ------------------------------------------------------------------- launchers --
+
+static inline int blocks_for(int n, int threads) { return n > 0 ? (n + threads - 1) / threads : 1; }
+
+static int reduce_grid(int n)
+{
+  int grid = globals().sm_count * 4;
+  int need = blocks_for(n, 256);
+  return grid < need ? grid : need;
+}
+
+static void ensure_partials(PfCtx *c, int count)
+{
+  if (count <= c->partials_cap) return;
+  if (c->d_partials) cudaFree(c->d_partials);
+  c->partials_cap = count;
+  AMCL_CUDA(cudaMalloc(&c->d_partials, sizeof(double) * (size_t)count));
+}
+
+static void sync_ints(PfCtx *c, int first, int count)
+{
+  AMCL_CUDA(cudaMemcpyAsync(c->h_ints + first, c->d_ints + first, sizeof(int) * (size_t)count,
+                            cudaMemcpyDeviceToHost, globals().stream));
+  AMCL_CUDA(cudaStreamSynchronize(globals().stream));
+}
+
+static void sync_scalars(PfCtx *c, int first, int count)
+{
+  AMCL_CUDA(cudaMemcpyAsync(c->h_scalars + first, c->d_scalars + first, sizeof(double) * (size_t)count,
+                            cudaMemcpyDeviceToHost, globals().stream));
+  AMCL_CUDA(cudaStreamSynchronize(globals().stream));
+}
+
+// d_ints slots
+enum { I_DISTINCT = 0, I_CUT = 1, I_CLUSTERS = 2, I_OUTSIDE = 3 };
+
+static void bin_sizes(const pf_sample_set_t *set, double *bx, double *by, double *bt)
+{
+  *bx = set->kdtree->size[0];
+  *by = set->kdtree->size[1];
+  *bt = set->kdtree->size[2];
+}
+
+// Histogram over samples [0, count) of `which` from precomputed keys.
+static void build_histogram(PfCtx *c, int count)
+{
+  cudaStream_t st = globals().stream;
+  AMCL_CUDA(cudaMemsetAsync(c->d_hash, 0xFF, sizeof(HashSlot) * (size_t)c->hash_cap, st));
+  hash_insert<<<blocks_for(count, 256), 256, 0, st>>>(c->d_keys, count, c->d_hash,
+                                                      c->hash_cap - 1, c->d_slot);
+  AMCL_LAUNCH_CHECK();
+  mark_first<<<blocks_for(count, 256), 256, 0, st>>>(c->d_hash, c->d_slot, count, c->d_flag);
+  AMCL_LAUNCH_CHECK();
+}
+
+// Labels + statistics for samples [0, n) of set `which`; the histogram
+// (d_keys/d_slot/d_flag/d_hash) must describe at least those samples.
+static void cluster_and_stats(PfCtx *c, int which, int n)
+{
+  cudaStream_t st = globals().stream;
+  pf_t *pf = c->host;
+  pf_sample_set_t *set = pf->sets + which;
+  unsigned int *cmin = c->d_scan + c->max_samples;  // second half: per-slot scratch (hash_cap)
+  const int nb = blocks_for(n, 256);
+
+  cc_init<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin);
+  AMCL_LAUNCH_CHECK();
+  cc_link<<<nb, 256, 0, st>>>(c->d_hash, c->hash_cap - 1, c->d_slot, c->d_flag, n);
+  AMCL_LAUNCH_CHECK();
+  cc_roots<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin);
+  AMCL_LAUNCH_CHECK();
+  // cluster-opening flags reuse d_keys' storage as u32 scratch (keys are spent)
+  unsigned int *cflag = reinterpret_cast<unsigned int *>(c->d_keys);
+  unsigned int *cscan = cflag + c->max_samples;
+  cc_mark_cluster_first<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin, cflag);
+  AMCL_LAUNCH_CHECK();
+  scan_u32(c, cflag, cscan, n, I_CLUSTERS);
+  cc_assign_ids<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, cflag, cscan, n, cmin);
+  AMCL_LAUNCH_CHECK();
+  sync_ints(c, I_CLUSTERS, 1);
+  const int ncl = c->h_ints[I_CLUSTERS];
+
+  if (ncl > c->cluster_acc_cap)
+  {
+    if (c->d_cluster_acc) cudaFree(c->d_cluster_acc);
+    c->cluster_acc_cap = ncl + ncl / 2 + 64;
+    AMCL_CUDA(cudaMalloc(&c->d_cluster_acc, sizeof(double) * 10 * (size_t)c->cluster_acc_cap));
+  }
+  AMCL_CUDA(cudaMemsetAsync(c->d_cluster_acc, 0, sizeof(double) * 10 * (size_t)(ncl > 0 ? ncl : 1), st));
+  cluster_accumulate<<<nb, 256, 0, st>>>(c->d_set[which], n, c->d_hash, c->d_slot, cmin,
+                                         c->d_cluster_acc, c->d_label);
+  AMCL_LAUNCH_CHECK();
+  std::vector<double> acc((size_t)10 * (ncl > 0 ? ncl : 1));
+  AMCL_CUDA(cudaMemcpyAsync(acc.data(), c->d_cluster_acc, sizeof(double) * 10 * (size_t)ncl,
+                            cudaMemcpyDeviceToHost, st));
+  AMCL_CUDA(cudaStreamSynchronize(st));
+
+  // pf.c:576-589 zeroes every slot; here only the ones that were in use
+  const int prev = set->cluster_count;
+  int limit = ncl < set->cluster_max_count ? ncl : set->cluster_max_count;
+  for (int k = limit; k < prev && k < set->cluster_max_count; k++)
+    memset(set->clusters + k, 0, sizeof(pf_cluster_t));
+  set->cluster_count = limit;
+
+  double m[4] = {0, 0, 0, 0}, cc[2][2] = {{0, 0}, {0, 0}}, weight = 0.0;
+  for (int k = 0; k < ncl; k++)
+  {
+    const double *a = acc.data() + (size_t)10 * k;
+    weight += a[1];
+    for (int q = 0; q < 4; q++) m[q] += a[2 + q];
+    cc[0][0] += a[6]; cc[0][1] += a[7]; cc[1][0] += a[8]; cc[1][1] += a[9];
+    if (k >= limit) continue;   // pf.c:609-610
+    pf_cluster_t *cl = set->clusters + k;
+    cl->count = (int)a[0];
+    cl->weight = a[1];
+    for (int q = 0; q < 4; q++) cl->m[q] = a[2 + q];
+    cl->c[0][0] = a[6]; cl->c[0][1] = a[7]; cl->c[1][0] = a[8]; cl->c[1][1] = a[9];
+    // pf.c:646-666
+    cl->mean.v[0] = cl->m[0] / cl->weight;
+    cl->mean.v[1] = cl->m[1] / cl->weight;
+    cl->mean.v[2] = atan2(cl->m[3], cl->m[2]);
+    cl->cov = pf_matrix_zero();
+    for (int j = 0; j < 2; j++)
+      for (int q = 0; q < 2; q++)
+        cl->cov.m[j][q] = cl->c[j][q] / cl->weight - cl->mean.v[j] * cl->mean.v[q];
+    cl->cov.m[2][2] = -2 * log(sqrt(cl->m[2] * cl->m[2] + cl->m[3] * cl->m[3]) / cl->weight);
+  }
+  set->mean = pf_vector_zero();
+  set->cov = pf_matrix_zero();
+  if (fabs(weight) < DBL_EPSILON)
+  {
+    printf("ERROR : divide-by-zero exception : weight is zero\n");   // pf.c:672-677
+    return;
+  }
+  // pf.c:678-690
+  set->mean.v[0] = m[0] / weight;
+  set->mean.v[1] = m[1] / weight;
+  set->mean.v[2] = atan2(m[3], m[2]);
+  for (int j = 0; j < 2; j++)
+    for (int q = 0; q < 2; q++)
+      set->cov.m[j][q] = cc[j][q] / weight - set->mean.v[j] * set->mean.v[q];
+  set->cov.m[2][2] = -2 * log(sqrt(m[2] * m[2] + m[3] * m[3]));
+}
+
+void run_cluster_stats(PfCtx *c, int which, bool histogram_ready)
+{
+  cudaStream_t st = globals().stream;
+  pf_sample_set_t *set = c->host->sets + which;
+  const int n = set->sample_count;
+  if (!histogram_ready)
+  {
+    double bx, by, bt;
+    bin_sizes(set, &bx, &by, &bt);
+    keys_of_set<<<blocks_for(n, 256), 256, 0, st>>>(c->d_set[which], n, c->d_keys, bx, by, bt);
+    AMCL_LAUNCH_CHECK();
+    build_histogram(c, n);
+    scan_u32(c, c->d_flag, c->d_scan, n, I_DISTINCT);
+    sync_ints(c, I_DISTINCT, 1);
+    set->kdtree->leaf_count = c->h_ints[I_DISTINCT];
+  }
+  cluster_and_stats(c, which, n);
+}
+
+int run_update_converged(PfCtx *c, int which)
+{
+  cudaStream_t st = globals().stream;
+  pf_t *pf = c->host;
+  pf_sample_set_t *set = pf->sets + which;
+  const int n = set->sample_count;
+  const int grid = reduce_grid(n);
+  ensure_partials(c, 2 * grid);
+  sum_xy<<<grid, 256, 0, st>>>(c->d_set[which], n, c->d_partials, c->d_partials + grid);
+  AMCL_LAUNCH_CHECK();
+  finish_xy<<<1, 256, 0, st>>>(c->d_partials, c->d_partials + grid, grid, n, c->d_scalars + 4);
+  AMCL_LAUNCH_CHECK();
+  AMCL_CUDA(cudaMemsetAsync(c->d_ints + I_OUTSIDE, 0, sizeof(int), st));
+  any_outside<<<grid, 256, 0, st>>>(c->d_set[which], n, c->d_scalars + 4, pf->dist_threshold,
+                                    c->d_ints + I_OUTSIDE);
+  AMCL_LAUNCH_CHECK();
+  sync_ints(c, I_OUTSIDE, 1);
+  const int conv = c->h_ints[I_OUTSIDE] ? 0 : 1;
+  set->converged = conv;
+  pf->converged = conv;
+  return conv;
+}
+
+void run_cep_stats(PfCtx *c, int which, double out[4])
+{
+  cudaStream_t st = globals().stream;
+  pf_sample_set_t *set = c->host->sets + which;
+  const int n = set->sample_count;
+  const int grid = reduce_grid(n);
+  ensure_partials(c, 4 * grid);
+  cep_sums<<<grid, 256, 0, st>>>(c->d_set[which], n, c->d_partials, grid);
+  AMCL_LAUNCH_CHECK();
+  finish_multi<<<1, 256, 0, st>>>(c->d_partials, grid, grid, 4, c->d_scalars + 8);
+  AMCL_LAUNCH_CHECK();
+  sync_scalars(c, 8, 4);
+  for (int q = 0; q < 4; q++) out[q] = c->h_scalars[8 + q];   // mn, mx, my, mrr
+}
+
+// copy_set (pf.c:321-360): b = a with weights renormalised by their sum.
+void run_copy_set(PfCtx *c, int from, int to)
+{
+  cudaStream_t st = globals().stream;
+  pf_t *pf = c->host;
+  const int n = pf->sets[from].sample_count;
+  const int grid = reduce_grid(n);
+  ensure_partials(c, grid);
+  sum_weights<<<grid, 256, 0, st>>>(c->d_set[from], n, c->d_partials);
+  AMCL_LAUNCH_CHECK();
+  finish_multi<<<1, 256, 0, st>>>(c->d_partials, grid, grid, 1, c->d_scalars + 12);
+  AMCL_LAUNCH_CHECK();
+  copy_scaled<<<blocks_for(n, 256), 256, 0, st>>>(c->d_set[from], c->d_set[to], n,
+                                                  c->d_scalars + 12);
+  AMCL_LAUNCH_CHECK();
+  pf->sets[to].sample_count = n;
+  pf->sets[to].converged = pf->sets[from].converged;
+  c->host_fresh[to] = false;
+}
+
+// pf_update_resample (pf.c:363-510)
+void run_resample(PfCtx *c)
+{
+  cudaStream_t st = globals().stream;
+  pf_t *pf = c->host;
+  const int ia = pf->current_set, ib = (pf->current_set + 1) % 2;
+  pf_sample_set_t *set_a = pf->sets + ia, *set_b = pf->sets + ib;
+  const int n_a = set_a->sample_count;
+  const int maxs = pf->max_samples;
+
+  // pf.c:378-394
+  if (pf->selective_resampling != 0 && set_a->n_effective > 0.5 * (set_a->sample_count))
+  {
+    run_copy_set(c, ia, ib);
+    run_cluster_stats(c, ib, false);
+    pf->current_set = ib;
+    return;
+  }
+
+  exact_cumsum(c, c->d_set[ia], n_a, c->d_cum);
+
+  // pf.c:411-413
+  double w_diff = 1.0 - pf->w_fast / pf->w_slow;
+  if (w_diff < 0.0) w_diff = 0.0;
+
+  // ---- draws for every candidate sample -----------------------------------
+  std::vector<int> inject_slot;
+  std::vector<Particle> injected;
+  unsigned short saved_state[3] = {0, 0, 0};
+  const bool host_stream = globals().rng == RNG_DRAND48;
+  if (host_stream)
+  {
+    // Draw exactly as pf.c:426-460 would for a full run to max_samples, then
+    // rewind and re-consume only what the first n samples used (below).
+    unsigned short probe[3] = {0, 0, 0};
+    unsigned short *old = seed48(probe);
+    memcpy(saved_state, old, sizeof(saved_state));
+    seed48(saved_state);
+    std::vector<double> draws((size_t)2 * maxs);
+    for (int m = 0; m < maxs; m++)
+    {
+      const double u = drand48();
+      draws[2 * (size_t)m] = u;
+      if (u < w_diff)
+      {
+        if (inject_slot.empty()) inject_slot.assign(maxs, -1);
+        const pf_vector_t p = (pf->random_pose_fn)(pf->random_pose_data);
+        inject_slot[m] = (int)injected.size();
+        Particle q; q.x = p.v[0]; q.y = p.v[1]; q.th = p.v[2]; q.w = 1.0;
+        injected.push_back(q);
+        draws[2 * (size_t)m + 1] = 0.0;
+      }
+      else
+        draws[2 * (size_t)m + 1] = drand48();
+    }
+    AMCL_CUDA(cudaMemcpyAsync(c->d_draws, draws.data(), sizeof(double) * 2 * (size_t)maxs,
+                              cudaMemcpyHostToDevice, st));
+    AMCL_CUDA(cudaStreamSynchronize(st));
+  }
+  else
+  {
+    const uint64_t key = globals().philox_seed ^ (0xA0761D6478BD642Full * (++c->step));
+    philox_resample_draws<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_draws, maxs, key);
+    AMCL_LAUNCH_CHECK();
+    if (w_diff > 0.0)
+    {
+      // recovery path: candidates with u < w_diff take a host-generated pose
+      std::vector<double> draws((size_t)2 * maxs);
+      AMCL_CUDA(cudaMemcpyAsync(draws.data(), c->d_draws, sizeof(double) * 2 * (size_t)maxs,
+                                cudaMemcpyDeviceToHost, st));
+      AMCL_CUDA(cudaStreamSynchronize(st));
+      for (int m = 0; m < maxs; m++)
+        if (draws[2 * (size_t)m] < w_diff)
+        {
+          if (inject_slot.empty()) inject_slot.assign(maxs, -1);
+          const pf_vector_t p = (pf->random_pose_fn)(pf->random_pose_data);
+          inject_slot[m] = (int)injected.size();
+          Particle q; q.x = p.v[0]; q.y = p.v[1]; q.th = p.v[2]; q.w = 1.0;
+          injected.push_back(q);
+        }
+    }
+  }
+
+  Particle *d_injected = nullptr;
+  int *d_inject_slot = nullptr;
+  if (!injected.empty())
+  {
+    AMCL_CUDA(cudaMalloc(&d_injected, sizeof(Particle) * injected.size()));
+    AMCL_CUDA(cudaMalloc(&d_inject_slot, sizeof(int) * (size_t)maxs));
+    AMCL_CUDA(cudaMemcpyAsync(d_injected, injected.data(), sizeof(Particle) * injected.size(),
+                              cudaMemcpyHostToDevice, st));
+    AMCL_CUDA(cudaMemcpyAsync(d_inject_slot, inject_slot.data(), sizeof(int) * (size_t)maxs,
+                              cudaMemcpyHostToDevice, st));
+  }
+
+  // ---- pick sources, copy poses, bin keys -----------------------------------
+  PickArgs pa;
+  pa.src = c->d_set[ia];
+  pa.n_src = n_a;
+  pa.cum = c->d_cum;
+  pa.draws = c->d_draws;
+  pa.injected = d_injected;
+  pa.inject_slot = d_inject_slot;
+  pa.dst = c->d_set[ib];
+  pa.src_index = c->d_src;
+  pa.keys = c->d_keys;
+  pa.count = maxs;
+  bin_sizes(set_b, &pa.bin_x, &pa.bin_y, &pa.bin_t);
+  pick_and_copy<<<blocks_for(maxs, 256), 256, 0, st>>>(pa);
+  AMCL_LAUNCH_CHECK();
+
+  // ---- histogram, k_m, KLD cut ---------------------------------------------
+  build_histogram(c, maxs);
+  scan_u32(c, c->d_flag, c->d_scan, maxs, I_DISTINCT);
+  c->h_ints[I_CUT] = maxs;
+  AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_CUT, c->h_ints + I_CUT, sizeof(int),
+                            cudaMemcpyHostToDevice, st));
+  find_kld_cut<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_scan, maxs, pf->min_samples, maxs,
+                                                      pf->pop_err, pf->pop_z, c->d_ints + I_CUT);
+  AMCL_LAUNCH_CHECK();
+  sync_ints(c, I_CUT, 1);
+  const int n = c->h_ints[I_CUT];
+  // leaf_count = k_{n-1}
+  unsigned int k_at_cut = 0;
+  AMCL_CUDA(cudaMemcpyAsync(&k_at_cut, c->d_scan + (n - 1), sizeof(unsigned int),
+                            cudaMemcpyDeviceToHost, st));
+  AMCL_CUDA(cudaStreamSynchronize(st));
+  set_b->sample_count = n;
+  set_b->kdtree->leaf_count = (int)k_at_cut;
+
+  if (d_injected)
+  {
+    cudaFree(d_injected);
+    cudaFree(d_inject_slot);
+  }
+
+  if (host_stream)
+  {
+    // leave libc's stream where the reference would have left it: replay the
+    // first n samples' draws from the saved state
+    seed48(saved_state);
+    for (int m = 0; m < n; m++)
+    {
+      if (drand48() < w_diff) (void)(pf->random_pose_fn)(pf->random_pose_data);
+      else (void)drand48();
+    }
+  }
+  c->draws_used = 2ull * (unsigned long long)n;
+
+  // pf.c:487-489
+  if (w_diff > 0.0) pf->w_slow = pf->w_fast = 0.0;
+
+  // pf.c:493-498: every weight is 1/n
+  set_uniform_weight<<<blocks_for(n, 256), 256, 0, st>>>(c->d_set[ib], n, 1.0 / (double)n);
+  AMCL_LAUNCH_CHECK();
+  c->host_fresh[ib] = false;
+
+  // pf.c:501-506
+  cluster_and_stats(c, ib, n);
+  pf->current_set = ib;
+  run_update_converged(c, ib);
+}
+
+}  // namespace amclb200

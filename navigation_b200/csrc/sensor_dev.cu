@@ -1,0 +1,943 @@
+// sensor_dev.cu -- the three laser measurement models of
+// /root/reference/amcl/src/amcl/sensors/amcl_laser.cpp on the device, and the
+// weight normalisation of pf_update_sensor (/root/reference/amcl/src/amcl/pf/pf.c:268-318).
+//
+// Work decomposition (all three models): ONE WARP PER PARTICLE, LANES OVER
+// BEAMS.  Neighbouring beams of one scan end in neighbouring cells, so the 32
+// gathers of one warp instruction fall into a handful of 32-byte sectors of the
+// 4x4-tiled distance-code map (context.hpp) instead of 32 unrelated ones; the
+// per-particle sum is a warp-shuffle reduction; the scan table and the
+// code -> likelihood table are staged once per CTA in shared memory by a bulk
+// (TMA) copy.
+//
+// Arithmetic: fp64 throughout (H6 in SURVEY.md: fp32 end points flip cells).
+// cos/sin(theta + bearing) come from one sincos per particle and the angle
+// addition formulas with host-computed cos/sin(bearing); cell coordinates are
+// formed directly in cell units.  Both change end points by a few ulp only
+// (cell flips ~1e-12 per beam), inside the 1e-5 weight tolerance.
+#include <math.h>
+#include <float.h>
+#include <string.h>
+
+#include <vector>
+
+#include "amcl/sensors/amcl_laser.h"
+#include "context.hpp"
+
+namespace amclb200
+{
+
+// ------------------------------------------------------------ bulk staging --
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p)
+{
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// Thread 0 arms an mbarrier with the byte count and issues 1-D bulk copies
+// (cp.async.bulk, the TMA engine); every thread then waits on the barrier.
+__device__ __forceinline__ void bulk_stage_begin(uint64_t *bar, uint32_t total_bytes)
+{
+  if (threadIdx.x == 0)
+  {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(bar)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)),
+                 "r"(total_bytes)
+                 : "memory");
+  }
+}
+
+__device__ __forceinline__ void bulk_stage_copy(void *dst, const void *src, uint32_t bytes,
+                                                uint64_t *bar)
+{
+  // bytes: multiple of 16; dst/src 16-byte aligned.  Called by thread 0 only.
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_addr(dst)),
+      "l"(src), "r"(bytes), "r"(smem_addr(bar))
+      : "memory");
+}
+
+__device__ __forceinline__ void bulk_stage_wait(uint64_t *bar)
+{
+  uint32_t done = 0;
+  const uint32_t a = smem_addr(bar);
+  while (!done)
+  {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(a)
+        : "memory");
+  }
+}
+
+// --------------------------------------------------- likelihood-field kernels --
+
+struct LfArgs
+{
+  Particle *set;
+  int n;
+  const double2 *beams;     // (r cos b / scale, r sin b / scale) per used beam
+  int nb;                   // number of used beams
+  int nb_pad;               // rounded up to an even count (16-byte granules)
+  const double *lut;        // code -> pz^3 (LF) | log pz (LFP); [ncodes_pad]
+  const unsigned char *agree;  // code -> z < beam_skip_distance (COUNT mode)
+  int ncodes_pad;
+  int code_offmap;          // table index used for off-map end points
+  const uint16_t *code;     // tiled distance codes
+  int tiles_x, sx, sy;
+  double lx, ly, la;        // laser pose in the robot frame
+  double ox, oy, scale;     // map origin (centre) and resolution
+  double half_x, half_y;    // 0.5 + size/2, folded into the cell coordinate
+  double *block_totals;     // one partial per CTA
+  int *beam_counts;         // COUNT mode: agreements per used beam
+};
+
+enum { MODE_LF = 0, MODE_LFP = 1, MODE_COUNT = 2 };
+
+constexpr int kSensorThreads = 256;
+constexpr double kCellGuard = 536870912.0;  // 2^29: beyond this nothing is on a map
+
+template <int MODE, bool LUT_IN_SMEM>
+__global__ void __launch_bounds__(kSensorThreads)
+likelihood_field_kernel(const LfArgs a)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double2 *s_beams = reinterpret_cast<double2 *>(smem_raw);
+  double *s_lut = reinterpret_cast<double *>(smem_raw + (size_t)a.nb_pad * sizeof(double2));
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ double s_red[kSensorThreads / 32];
+  int *s_counts = nullptr;
+
+  const uint32_t beam_bytes = (uint32_t)a.nb_pad * (uint32_t)sizeof(double2);
+  const uint32_t lut_bytes = LUT_IN_SMEM ? (uint32_t)a.ncodes_pad * 8u : 0u;
+  bulk_stage_begin(&s_bar, beam_bytes + lut_bytes);
+  if (threadIdx.x == 0)
+  {
+    bulk_stage_copy(s_beams, a.beams, beam_bytes, &s_bar);
+    if (LUT_IN_SMEM) bulk_stage_copy(s_lut, a.lut, lut_bytes, &s_bar);
+  }
+  if (MODE == MODE_COUNT)
+  {
+    s_counts = reinterpret_cast<int *>(smem_raw + (size_t)a.nb_pad * sizeof(double2) + lut_bytes);
+    for (int k = threadIdx.x; k < a.nb; k += blockDim.x) s_counts[k] = 0;
+  }
+  __syncthreads();  // barrier init visible to all before anyone polls it
+  bulk_stage_wait(&s_bar);
+
+  const double *lut = LUT_IN_SMEM ? s_lut : a.lut;
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = blockDim.x >> 5;
+  const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  const int warp_stride = gridDim.x * warps_per_block;
+  double warp_total = 0.0;  // meaningful in lane 0
+
+  for (int p = warp_global; p < a.n; p += warp_stride)
+  {
+    const Particle s = load_particle(a.set + p);
+    // pf_vector_coord_add(laser_pose, pose) (pf_vector.c:106-116); only the
+    // sine and cosine of the summed heading are needed below.
+    double sn, cs;
+    sincos(s.th, &sn, &cs);
+    const double px = s.x + a.lx * cs - a.ly * sn;
+    const double py = s.y + a.lx * sn + a.ly * cs;
+    double st = sn, ct = cs;
+    if (a.la != 0.0) sincos(s.th + a.la, &st, &ct);
+    // MAP_GXWX / MAP_GYWY (map.h:137-138) in cell units, size/2 folded in
+    double X0 = (px - a.ox) / a.scale + a.half_x;
+    double Y0 = (py - a.oy) / a.scale + a.half_y;
+    const bool sane = fabs(X0) < kCellGuard && fabs(Y0) < kCellGuard;
+    if (!sane) { X0 = -kCellGuard; Y0 = -kCellGuard; st = 0.0; ct = 0.0; }
+
+    double acc0 = 0.0, acc1 = 0.0;
+    for (int i = lane; i < a.nb; i += 64)
+    {
+      const int i1 = i + 32;
+      const bool has1 = i1 < a.nb;
+      const double2 b0 = s_beams[i];
+      const double2 b1 = s_beams[has1 ? i1 : i];
+      const int mi0 = floor_to_int(fma(ct, b0.x, fma(-st, b0.y, X0)));
+      const int mj0 = floor_to_int(fma(st, b0.x, fma(ct, b0.y, Y0)));
+      const int mi1 = floor_to_int(fma(ct, b1.x, fma(-st, b1.y, X0)));
+      const int mj1 = floor_to_int(fma(st, b1.x, fma(ct, b1.y, Y0)));
+      int c0 = a.code_offmap, c1 = a.code_offmap;
+      if ((unsigned)mi0 < (unsigned)a.sx && (unsigned)mj0 < (unsigned)a.sy)
+        c0 = __ldg(a.code + ((size_t)((mj0 >> 2) * a.tiles_x + (mi0 >> 2)) << 4) +
+                   ((mj0 & 3) << 2) + (mi0 & 3));
+      if ((unsigned)mi1 < (unsigned)a.sx && (unsigned)mj1 < (unsigned)a.sy)
+        c1 = __ldg(a.code + ((size_t)((mj1 >> 2) * a.tiles_x + (mi1 >> 2)) << 4) +
+                   ((mj1 & 3) << 2) + (mi1 & 3));
+      if (MODE == MODE_COUNT)
+      {
+        if (a.agree[c0]) atomicAdd(&s_counts[i], 1);
+        if (has1 && a.agree[c1]) atomicAdd(&s_counts[i1], 1);
+      }
+      else
+      {
+        acc0 += lut[c0];
+        if (has1) acc1 += lut[c1];
+      }
+    }
+    if (MODE != MODE_COUNT)
+    {
+      const double sum = warp_sum(acc0 + acc1);
+      if (lane == 0)
+      {
+        // LF : p = 1 + sum pz^3          (amcl_laser.cpp:241,295,298)
+        // LFP: weight *= exp(sum log pz)  (amcl_laser.cpp:437,444)
+        const double factor = MODE == MODE_LF ? 1.0 + sum : exp(sum);
+        const double w = s.w * factor;
+        a.set[p].w = w;
+        warp_total += w;
+      }
+    }
+  }
+
+  if (MODE == MODE_COUNT)
+  {
+    __syncthreads();
+    for (int k = threadIdx.x; k < a.nb; k += blockDim.x)
+      if (s_counts[k]) atomicAdd(&a.beam_counts[k], s_counts[k]);
+  }
+  else
+  {
+    const double t = block_sum(lane == 0 ? warp_total : 0.0, s_red);
+    if (threadIdx.x == 0) a.block_totals[blockIdx.x] = t;
+  }
+}
+
+// Sums `count` partials in index order with one block; out[slot] = sum.
+__global__ void finish_partials(const double *__restrict__ partials, int count,
+                                double *__restrict__ out, int slot)
+{
+  __shared__ double s_red[32];
+  double v = 0.0;
+  for (int k = threadIdx.x; k < count; k += blockDim.x) v += partials[k];
+  const double t = block_sum(v, s_red);
+  if (threadIdx.x == 0) out[slot] = t;
+}
+
+// ----------------------------------------------------------- beam model kernel --
+
+struct BeamArgs
+{
+  Particle *set;
+  int n;
+  const double *tab;        // 5 doubles per beam: range, cos b, sin b, short term, tail term
+  int nb;
+  const uint64_t *blocked;  // 8x8 bit tiles
+  int btx, sx, sy;
+  double lx, ly, la;
+  double ox, oy, scale;
+  double range_max;
+  double z_hit, hit_denom;  // 2 sigma^2
+  double *block_totals;
+};
+
+// map_calc_range (map_range.c:38-120) on the bit-tiled occupancy: returns the
+// range in metres.  The current 8x8 tile word is cached in a register.
+__device__ __forceinline__ double cast_ray(const BeamArgs &a, int x0, int y0, int x1, int y1)
+{
+  const bool steep = abs(y1 - y0) > abs(x1 - x0);
+  if (steep)
+  {
+    int t = x0; x0 = y0; y0 = t;
+    t = x1; x1 = y1; y1 = t;
+  }
+  const int dx = abs(x1 - x0), dy = abs(y1 - y0);
+  const int xs = x0 < x1 ? 1 : -1, ys = y0 < y1 ? 1 : -1;
+  int x = x0, y = y0, err = 0;
+  int cur_tile = -1;
+  uint64_t word = 0;
+  for (;;)
+  {
+    const int ci = steep ? y : x, cj = steep ? x : y;
+    bool stop = !((unsigned)ci < (unsigned)a.sx && (unsigned)cj < (unsigned)a.sy);
+    if (!stop)
+    {
+      const int tile = (cj >> 3) * a.btx + (ci >> 3);
+      if (tile != cur_tile)
+      {
+        cur_tile = tile;
+        word = __ldg(a.blocked + tile);
+      }
+      stop = (word >> (((cj & 7) << 3) | (ci & 7))) & 1ull;
+    }
+    if (stop)
+    {
+      const int ddx = x - x0, ddy = y - y0;
+      return sqrt((double)((long long)ddx * ddx + (long long)ddy * ddy)) * a.scale;
+    }
+    if (x == x1 + xs) return a.range_max;
+    x += xs;
+    err += dy;
+    if (2 * err >= dx)
+    {
+      y += ys;
+      err -= dx;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kSensorThreads) beam_model_kernel(const BeamArgs a)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double *s_tab = reinterpret_cast<double *>(smem_raw);
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ double s_red[kSensorThreads / 32];
+  const uint32_t bytes = (uint32_t)(((size_t)a.nb * 5 * 8 + 15) & ~(size_t)15);
+  bulk_stage_begin(&s_bar, bytes);
+  if (threadIdx.x == 0) bulk_stage_copy(s_tab, a.tab, bytes, &s_bar);
+  __syncthreads();
+  bulk_stage_wait(&s_bar);
+
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = blockDim.x >> 5;
+  const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  const int warp_stride = gridDim.x * warps_per_block;
+  double warp_total = 0.0;
+
+  for (int p = warp_global; p < a.n; p += warp_stride)
+  {
+    const Particle s = load_particle(a.set + p);
+    double sn, cs;
+    sincos(s.th, &sn, &cs);
+    const double px = s.x + a.lx * cs - a.ly * sn;
+    const double py = s.y + a.lx * sn + a.ly * cs;
+    double st = sn, ct = cs;
+    if (a.la != 0.0) sincos(s.th + a.la, &st, &ct);
+    const double fx0 = floor((px - a.ox) / a.scale + 0.5), fy0 = floor((py - a.oy) / a.scale + 0.5);
+    const bool sane = fabs(fx0) < kCellGuard && fabs(fy0) < kCellGuard;
+    const int x0 = sane ? (int)fx0 + a.sx / 2 : -1;
+    const int y0 = sane ? (int)fy0 + a.sy / 2 : -1;
+
+    double acc = 0.0;
+    for (int i = lane; i < a.nb; i += 32)
+    {
+      const double *t = s_tab + 5 * i;
+      const double obs_range = t[0];
+      const double cdir = ct * t[1] - st * t[2];   // cos(theta + bearing)
+      const double sdir = st * t[1] + ct * t[2];
+      const double ex = floor((px + a.range_max * cdir - a.ox) / a.scale + 0.5);
+      const double ey = floor((py + a.range_max * sdir - a.oy) / a.scale + 0.5);
+      const int x1 = (int)fmin(fmax(ex, -kCellGuard), kCellGuard) + a.sx / 2;
+      const int y1 = (int)fmin(fmax(ey, -kCellGuard), kCellGuard) + a.sy / 2;
+      const double map_range = cast_ray(a, x0, y0, x1, y1);
+      // amcl_laser.cpp:179-196
+      const double z = obs_range - map_range;
+      double pz = a.z_hit * exp(-(z * z) / a.hit_denom);
+      if (z < 0) pz += t[3];
+      pz += t[4];
+      acc += pz * pz * pz;
+    }
+    const double sum = warp_sum(acc);
+    if (lane == 0)
+    {
+      const double w = s.w * (1.0 + sum);
+      a.set[p].w = w;
+      warp_total += w;
+    }
+  }
+  const double tt = block_sum(lane == 0 ? warp_total : 0.0, s_red);
+  if (threadIdx.x == 0) a.block_totals[blockIdx.x] = tt;
+}
+
+// One thread per ray: the batched form of map_calc_range (map_range.c:38-120).
+__global__ void calc_ranges_kernel(const BeamArgs a, const double *__restrict__ rays, int n,
+                                   double *__restrict__ out)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double ox = rays[3 * (size_t)i], oy = rays[3 * (size_t)i + 1], oa = rays[3 * (size_t)i + 2];
+  const double fx0 = floor((ox - a.ox) / a.scale + 0.5), fy0 = floor((oy - a.oy) / a.scale + 0.5);
+  const double fx1 = floor((ox + a.range_max * cos(oa) - a.ox) / a.scale + 0.5);
+  const double fy1 = floor((oy + a.range_max * sin(oa) - a.oy) / a.scale + 0.5);
+  const int x0 = (int)fmin(fmax(fx0, -kCellGuard), kCellGuard) + a.sx / 2;
+  const int y0 = (int)fmin(fmax(fy0, -kCellGuard), kCellGuard) + a.sy / 2;
+  const int x1 = (int)fmin(fmax(fx1, -kCellGuard), kCellGuard) + a.sx / 2;
+  const int y1 = (int)fmin(fmax(fy1, -kCellGuard), kCellGuard) + a.sy / 2;
+  out[i] = cast_ray(a, x0, y0, x1, y1);
+}
+
+// ------------------------------------------------ normalisation (pf.c:282-316) --
+
+// total > 0: w /= total, accumulates sum w^2 per block.  total <= 0: w = 1/n.
+__global__ void normalise_weights(Particle *set, int n, double total, double uniform,
+                                  double *block_sq)
+{
+  __shared__ double s_red[32];
+  double sq = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+  {
+    double w;
+    if (total > 0.0)
+    {
+      w = set[i].w / total;
+      sq += w * w;
+    }
+    else
+      w = uniform;
+    set[i].w = w;
+  }
+  const double t = block_sum(sq, s_red);
+  if (threadIdx.x == 0) block_sq[blockIdx.x] = t;
+}
+
+// ------------------------------------------------------------------ launchers --
+
+static void ensure_partials(PfCtx *c, int count)
+{
+  if (count <= c->partials_cap) return;
+  if (c->d_partials) cudaFree(c->d_partials);
+  c->partials_cap = count;
+  AMCL_CUDA(cudaMalloc(&c->d_partials, sizeof(double) * (size_t)count));
+}
+
+static double read_scalar(PfCtx *c, int slot)
+{
+  AMCL_CUDA(cudaMemcpyAsync(c->h_scalars + slot, c->d_scalars + slot, sizeof(double),
+                            cudaMemcpyDeviceToHost, globals().stream));
+  AMCL_CUDA(cudaStreamSynchronize(globals().stream));
+  return c->h_scalars[slot];
+}
+
+template <typename K>
+static int persistent_grid(K kernel, int threads, size_t smem)
+{
+  int per_sm = 0;
+  if (smem > 48 * 1024)
+    AMCL_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  AMCL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
+  if (per_sm < 1) AMCL_FATAL("kernel does not fit an SM with %zu bytes of shared memory", smem);
+  return per_sm * globals().sm_count;
+}
+
+double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
+                            const double laser_pose[3], const LaserScanHost &scan,
+                            const std::vector<double> &lut, const int *mask_or_null,
+                            int n_beam_slots, int *agree_counts_or_null,
+                            const std::vector<unsigned char> *agree_lut)
+{
+  (void)n_beam_slots;
+  cudaStream_t st = globals().stream;
+  const int n = c->host->sets[which].sample_count;
+  // beam table: only beams that are integrated (mask applied on the host)
+  std::vector<double> tab;
+  std::vector<int> used;
+  for (size_t k = 0; k < scan.a.size(); k++)
+  {
+    if (mask_or_null && !mask_or_null[scan.beam_ind[k]]) continue;
+    tab.push_back(scan.a[k]);
+    tab.push_back(scan.b[k]);
+    used.push_back((int)k);
+  }
+  const int nb = (int)used.size();
+  const int nb_pad = (nb + 1) & ~1;
+  tab.resize((size_t)(nb_pad > 0 ? nb_pad : 2) * 2, 0.0);
+  const int ncodes = (int)lut.size();
+  const int ncodes_pad = (ncodes + 1) & ~1;
+  const bool count_mode = agree_counts_or_null != nullptr;
+
+  // device staging: [beams | lut | agree bytes | counts]
+  size_t need = tab.size() + (size_t)ncodes_pad;
+  if ((int)need > c->scan_tab_cap)
+  {
+    if (c->d_scan_tab) cudaFree(c->d_scan_tab);
+    c->scan_tab_cap = (int)need + 1024;
+    AMCL_CUDA(cudaMalloc(&c->d_scan_tab, sizeof(double) * (size_t)c->scan_tab_cap));
+  }
+  std::vector<double> stage(need, 0.0);
+  memcpy(stage.data(), tab.data(), tab.size() * sizeof(double));
+  memcpy(stage.data() + tab.size(), lut.data(), lut.size() * sizeof(double));
+  AMCL_CUDA(cudaMemcpyAsync(c->d_scan_tab, stage.data(), need * sizeof(double),
+                            cudaMemcpyHostToDevice, st));
+
+  unsigned char *d_agree = nullptr;
+  int *d_counts = nullptr;
+  if (count_mode)
+  {
+    size_t bytes = (size_t)ncodes_pad + sizeof(int) * (size_t)(nb + 1);
+    if ((int)bytes > c->lut_cap)
+    {
+      if (c->d_lut) cudaFree(c->d_lut);
+      c->lut_cap = (int)bytes + 4096;
+      AMCL_CUDA(cudaMalloc(&c->d_lut, (size_t)c->lut_cap));
+    }
+    d_counts = reinterpret_cast<int *>(c->d_lut);
+    d_agree = reinterpret_cast<unsigned char *>(c->d_lut) + sizeof(int) * (size_t)(nb + 1);
+    AMCL_CUDA(cudaMemsetAsync(d_counts, 0, sizeof(int) * (size_t)(nb + 1), st));
+    AMCL_CUDA(cudaMemcpyAsync(d_agree, agree_lut->data(), agree_lut->size(),
+                              cudaMemcpyHostToDevice, st));
+  }
+
+  LfArgs a;
+  a.set = c->d_set[which];
+  a.n = n;
+  a.beams = reinterpret_cast<const double2 *>(c->d_scan_tab);
+  a.nb = nb;
+  a.nb_pad = nb_pad > 0 ? nb_pad : 2;
+  a.lut = c->d_scan_tab + tab.size();
+  a.agree = d_agree;
+  a.ncodes_pad = ncodes_pad;
+  a.code_offmap = ncodes - 1;  // last entry: off-map end point
+  a.code = m->d_code;
+  a.tiles_x = m->tiles_x;
+  a.sx = m->sx;
+  a.sy = m->sy;
+  a.lx = laser_pose[0];
+  a.ly = laser_pose[1];
+  a.la = laser_pose[2];
+  a.ox = m->origin_x;
+  a.oy = m->origin_y;
+  a.scale = m->scale;
+  a.half_x = 0.5 + (double)(m->sx / 2);
+  a.half_y = 0.5 + (double)(m->sy / 2);
+  a.beam_counts = d_counts;
+
+  const size_t beam_bytes = (size_t)a.nb_pad * sizeof(double2);
+  const size_t lut_bytes = (size_t)ncodes_pad * 8;
+  const bool lut_smem = beam_bytes + lut_bytes + (count_mode ? sizeof(int) * (size_t)nb : 0) <= 96 * 1024;
+  const size_t smem = beam_bytes + (lut_smem ? lut_bytes : 0) + (count_mode ? sizeof(int) * (size_t)(nb + 1) : 0);
+
+  int grid;
+#define AMCL_LF_LAUNCH(MODE, INSMEM)                                                     \
+  do                                                                                     \
+  {                                                                                      \
+    grid = persistent_grid(likelihood_field_kernel<MODE, INSMEM>, kSensorThreads, smem); \
+    int need_blocks = (n + (kSensorThreads / 32) - 1) / (kSensorThreads / 32);           \
+    if (grid > need_blocks) grid = need_blocks > 0 ? need_blocks : 1;                    \
+    ensure_partials(c, grid);                                                            \
+    a.block_totals = c->d_partials;                                                      \
+    likelihood_field_kernel<MODE, INSMEM><<<grid, kSensorThreads, smem, st>>>(a);        \
+  } while (0)
+
+  if (count_mode)
+  {
+    if (lut_smem) AMCL_LF_LAUNCH(MODE_COUNT, true); else AMCL_LF_LAUNCH(MODE_COUNT, false);
+  }
+  else if (model == 1)
+  {
+    if (lut_smem) AMCL_LF_LAUNCH(MODE_LF, true); else AMCL_LF_LAUNCH(MODE_LF, false);
+  }
+  else
+  {
+    if (lut_smem) AMCL_LF_LAUNCH(MODE_LFP, true); else AMCL_LF_LAUNCH(MODE_LFP, false);
+  }
+#undef AMCL_LF_LAUNCH
+  AMCL_LAUNCH_CHECK();
+
+  if (count_mode)
+  {
+    std::vector<int> counts((size_t)nb + 1);
+    AMCL_CUDA(cudaMemcpyAsync(counts.data(), d_counts, sizeof(int) * (size_t)nb,
+                              cudaMemcpyDeviceToHost, st));
+    AMCL_CUDA(cudaStreamSynchronize(st));
+    for (int k = 0; k < nb; k++) agree_counts_or_null[scan.beam_ind[used[k]]] = counts[k];
+    return 0.0;
+  }
+  finish_partials<<<1, 256, 0, st>>>(c->d_partials, grid, c->d_scalars, 0);
+  AMCL_LAUNCH_CHECK();
+  const double total = read_scalar(c, 0);  // also orders the staging vectors' lifetime
+  c->host_fresh[which] = false;
+  return total;
+}
+
+double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3],
+                      const LaserScanHost &scan, double range_max, const double zp[6])
+{
+  cudaStream_t st = globals().stream;
+  const int n = c->host->sets[which].sample_count;
+  const int nb = (int)scan.range.size();
+  // zp: z_hit, z_short, z_max, z_rand, sigma_hit, lambda_short
+  std::vector<double> tab((size_t)(nb > 0 ? nb : 1) * 5 + 2, 0.0);
+  for (int k = 0; k < nb; k++)
+  {
+    const double r = scan.range[k];
+    tab[5 * k + 0] = r;
+    tab[5 * k + 1] = scan.cb[k];
+    tab[5 * k + 2] = scan.sb[k];
+    tab[5 * k + 3] = zp[1] * zp[5] * exp(-zp[5] * r);          // amcl_laser.cpp:185
+    double tail = 0.0;
+    if (r == range_max) tail += zp[2] * 1.0;                     // :189
+    if (r < range_max) tail += zp[3] * 1.0 / range_max;          // :193
+    tab[5 * k + 4] = tail;
+  }
+  if ((int)tab.size() > c->scan_tab_cap)
+  {
+    if (c->d_scan_tab) cudaFree(c->d_scan_tab);
+    c->scan_tab_cap = (int)tab.size() + 1024;
+    AMCL_CUDA(cudaMalloc(&c->d_scan_tab, sizeof(double) * (size_t)c->scan_tab_cap));
+  }
+  AMCL_CUDA(cudaMemcpyAsync(c->d_scan_tab, tab.data(), tab.size() * sizeof(double),
+                            cudaMemcpyHostToDevice, st));
+  BeamArgs a;
+  a.set = c->d_set[which];
+  a.n = n;
+  a.tab = c->d_scan_tab;
+  a.nb = nb;
+  a.blocked = m->d_blocked;
+  a.btx = m->btiles_x;
+  a.sx = m->sx;
+  a.sy = m->sy;
+  a.lx = laser_pose[0];
+  a.ly = laser_pose[1];
+  a.la = laser_pose[2];
+  a.ox = m->origin_x;
+  a.oy = m->origin_y;
+  a.scale = m->scale;
+  a.range_max = range_max;
+  a.z_hit = zp[0];
+  a.hit_denom = 2 * zp[4] * zp[4];
+  const size_t smem = ((size_t)nb * 5 * 8 + 15) & ~(size_t)15;
+  int grid = persistent_grid(beam_model_kernel, kSensorThreads, smem);
+  int need_blocks = (n + (kSensorThreads / 32) - 1) / (kSensorThreads / 32);
+  if (grid > need_blocks) grid = need_blocks > 0 ? need_blocks : 1;
+  ensure_partials(c, grid);
+  a.block_totals = c->d_partials;
+  beam_model_kernel<<<grid, kSensorThreads, smem, st>>>(a);
+  AMCL_LAUNCH_CHECK();
+  finish_partials<<<1, 256, 0, st>>>(c->d_partials, grid, c->d_scalars, 0);
+  AMCL_LAUNCH_CHECK();
+  const double total = read_scalar(c, 0);
+  c->host_fresh[which] = false;
+  return total;
+}
+
+void run_sensor_normalise(PfCtx *c, int which, double total)
+{
+  cudaStream_t st = globals().stream;
+  pf_t *pf = c->host;
+  pf_sample_set_t *set = pf->sets + which;
+  const int n = set->sample_count;
+  int grid = globals().sm_count * 4;
+  int need_blocks = (n + 255) / 256;
+  if (grid > need_blocks) grid = need_blocks > 0 ? need_blocks : 1;
+  ensure_partials(c, grid);
+  normalise_weights<<<grid, 256, 0, st>>>(c->d_set[which], n, total, 1.0 / n, c->d_partials);
+  AMCL_LAUNCH_CHECK();
+  double neff = 0.0;
+  if (total > 0.0)
+  {
+    finish_partials<<<1, 256, 0, st>>>(c->d_partials, grid, c->d_scalars, 1);
+    AMCL_LAUNCH_CHECK();
+    neff = read_scalar(c, 1);
+    // pf.c:293-302.  w_avg accumulates the very numbers the model summed into
+    // `total`, in the same order, so it equals total / n.
+    double w_avg = total / n;
+    if (pf->w_slow == 0.0) pf->w_slow = w_avg;
+    else pf->w_slow += pf->alpha_slow * (w_avg - pf->w_slow);
+    if (pf->w_fast == 0.0) pf->w_fast = w_avg;
+    else pf->w_fast += pf->alpha_fast * (w_avg - pf->w_fast);
+  }
+  set->n_effective = 1.0 / neff;  // pf.c:316 (1/0 -> inf on the zero-total path)
+  c->host_fresh[which] = false;
+}
+
+void run_calc_ranges(MapCtx *m, const double *rays_xya, int n, double max_range, double *out)
+{
+  cudaStream_t st = globals().stream;
+  if (n <= 0) return;
+  double *d_rays = nullptr, *d_out = nullptr;
+  AMCL_CUDA(cudaMalloc(&d_rays, sizeof(double) * 3 * (size_t)n));
+  AMCL_CUDA(cudaMalloc(&d_out, sizeof(double) * (size_t)n));
+  AMCL_CUDA(cudaMemcpyAsync(d_rays, rays_xya, sizeof(double) * 3 * (size_t)n,
+                            cudaMemcpyHostToDevice, st));
+  BeamArgs a;
+  memset(&a, 0, sizeof(a));
+  a.blocked = m->d_blocked;
+  a.btx = m->btiles_x;
+  a.sx = m->sx;
+  a.sy = m->sy;
+  a.ox = m->origin_x;
+  a.oy = m->origin_y;
+  a.scale = m->scale;
+  a.range_max = max_range;
+  calc_ranges_kernel<<<(n + 127) / 128, 128, 0, st>>>(a, d_rays, n, d_out);
+  AMCL_LAUNCH_CHECK();
+  AMCL_CUDA(cudaMemcpyAsync(out, d_out, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, st));
+  AMCL_CUDA(cudaStreamSynchronize(st));
+  cudaFree(d_rays);
+  cudaFree(d_out);
+}
+
+}  // namespace amclb200
+
+// ====================================================== amcl::AMCLLaser (C++) ==
+
+using namespace amclb200;
+
+namespace amcl
+{
+
+// The private block of AMCLLaser, reachable through the friend declaration in
+// the header.
+struct LaserAccess
+{
+  static int model(const AMCLLaser *l) { return (int)l->model_type; }
+  static map_t *map(const AMCLLaser *l) { return l->map; }
+  static int max_beams(const AMCLLaser *l) { return l->max_beams; }
+  static const pf_vector_t &pose(const AMCLLaser *l) { return l->laser_pose; }
+  static void params(const AMCLLaser *l, double zp[6])
+  {
+    zp[0] = l->z_hit; zp[1] = l->z_short; zp[2] = l->z_max;
+    zp[3] = l->z_rand; zp[4] = l->sigma_hit; zp[5] = l->lambda_short;
+  }
+  static bool is_ours(pf_sensor_model_fn_t fn)
+  {
+    return fn == (pf_sensor_model_fn_t)AMCLLaser::BeamModel ||
+           fn == (pf_sensor_model_fn_t)AMCLLaser::LikelihoodFieldModel ||
+           fn == (pf_sensor_model_fn_t)AMCLLaser::LikelihoodFieldModelProb;
+  }
+  static void skip(const AMCLLaser *l, bool *on, double v[3])
+  {
+    *on = l->do_beamskip;
+    v[0] = l->beam_skip_distance;
+    v[1] = l->beam_skip_threshold;
+    v[2] = l->beam_skip_error_threshold;
+  }
+};
+
+// pf_update_sensor must know whether a model function is one of ours (runs on
+// the device-resident set) or a foreign host callback (needs the host mirror).
+bool amclb200_is_device_laser_model(pf_sensor_model_fn_t fn)
+{
+  return LaserAccess::is_ours(fn);
+}
+
+// amcl_sensor.cpp:37-95
+AMCLSensor::AMCLSensor() {}
+AMCLSensor::~AMCLSensor() {}
+bool AMCLSensor::UpdateAction(pf_t *, AMCLSensorData *) { return false; }
+bool AMCLSensor::InitSensor(pf_t *, AMCLSensorData *) { return false; }
+bool AMCLSensor::UpdateSensor(pf_t *, AMCLSensorData *) { return false; }
+
+// amcl_laser.cpp:44-55
+AMCLLaser::AMCLLaser(size_t max_beams, map_t *map)
+    : AMCLSensor(), max_samples(0), max_obs(0), temp_obs(NULL)
+{
+  this->time = 0.0;
+  this->max_beams = max_beams;
+  this->map = map;
+  this->model_type = LASER_MODEL_BEAM;
+  this->do_beamskip = false;
+}
+
+// amcl_laser.cpp:56-64: nothing to release, temp_obs is never allocated here.
+AMCLLaser::~AMCLLaser() {}
+
+// amcl_laser.cpp:66-83
+void AMCLLaser::SetModelBeam(double z_hit, double z_short, double z_max, double z_rand,
+                             double sigma_hit, double lambda_short, double chi_outlier)
+{
+  this->model_type = LASER_MODEL_BEAM;
+  this->z_hit = z_hit;
+  this->z_short = z_short;
+  this->z_max = z_max;
+  this->z_rand = z_rand;
+  this->sigma_hit = sigma_hit;
+  this->lambda_short = lambda_short;
+  this->chi_outlier = chi_outlier;
+}
+
+// amcl_laser.cpp:85-97
+void AMCLLaser::SetModelLikelihoodField(double z_hit, double z_rand, double sigma_hit,
+                                        double max_occ_dist)
+{
+  this->model_type = LASER_MODEL_LIKELIHOOD_FIELD;
+  this->z_hit = z_hit;
+  this->z_rand = z_rand;
+  this->sigma_hit = sigma_hit;
+  map_update_cspace(this->map, max_occ_dist);
+}
+
+// amcl_laser.cpp:99-118
+void AMCLLaser::SetModelLikelihoodFieldProb(double z_hit, double z_rand, double sigma_hit,
+                                            double max_occ_dist, bool do_beamskip,
+                                            double beam_skip_distance,
+                                            double beam_skip_threshold,
+                                            double beam_skip_error_threshold)
+{
+  this->model_type = LASER_MODEL_LIKELIHOOD_FIELD_PROB;
+  this->z_hit = z_hit;
+  this->z_rand = z_rand;
+  this->sigma_hit = sigma_hit;
+  this->do_beamskip = do_beamskip;
+  this->beam_skip_distance = beam_skip_distance;
+  this->beam_skip_threshold = beam_skip_threshold;
+  this->beam_skip_error_threshold = beam_skip_error_threshold;
+  map_update_cspace(this->map, max_occ_dist);
+}
+
+// amcl_laser.cpp:496-510.  Kept for link compatibility; the device path needs
+// no per-(particle, beam) scratch, so this only records the sizes.
+void AMCLLaser::reallocTempData(int new_max_samples, int new_max_obs)
+{
+  max_obs = new_max_obs;
+  max_samples = new_max_samples > max_samples ? new_max_samples : max_samples;
+}
+
+// amcl_laser.cpp:123-139
+bool AMCLLaser::UpdateSensor(pf_t *pf, AMCLSensorData *data)
+{
+  if (this->max_beams < 2) return false;
+  if (this->model_type == LASER_MODEL_LIKELIHOOD_FIELD)
+    pf_update_sensor(pf, (pf_sensor_model_fn_t)LikelihoodFieldModel, data);
+  else if (this->model_type == LASER_MODEL_LIKELIHOOD_FIELD_PROB)
+    pf_update_sensor(pf, (pf_sensor_model_fn_t)LikelihoodFieldModelProb, data);
+  else
+    pf_update_sensor(pf, (pf_sensor_model_fn_t)BeamModel, data);
+  return true;
+}
+
+// Host-side preparation shared by the three models: walk the scan with the
+// reference's stride and skip rules and tabulate the per-beam constants.
+static void tabulate_scan(AMCLLaserData *data, int step, bool skip_invalid, double scale,
+                          LaserScanHost *out)
+{
+  int beam_ind = 0;
+  for (int i = 0; i < data->range_count; i += step, beam_ind++)
+  {
+    const double r = data->ranges[i][0], b = data->ranges[i][1];
+    if (skip_invalid)
+    {
+      if (r >= data->range_max) continue;   // amcl_laser.cpp:258-259, 383-385
+      if (r != r) continue;                 // :262-263, 388-390
+    }
+    const double cb = cos(b), sb = sin(b);
+    out->a.push_back(r * cb / scale);
+    out->b.push_back(r * sb / scale);
+    out->range.push_back(r);
+    out->cb.push_back(cb);
+    out->sb.push_back(sb);
+    out->beam_ind.push_back(beam_ind);
+  }
+}
+
+static MapCtx *ready_map(map_t *map, bool need_dist)
+{
+  MapCtx *m = map_ctx(map, true);
+  if (!m->occ_uploaded) map_upload_occupancy(m);
+  if (need_dist && !m->dist_valid)
+    AMCL_FATAL("likelihood-field model used before map_update_cspace()");
+  return m;
+}
+
+// amcl_laser.cpp:215-303
+double AMCLLaser::LikelihoodFieldModel(AMCLLaserData *data, pf_sample_set_t *set)
+{
+  AMCLLaser *self = (AMCLLaser *)data->sensor;
+  int which = 0;
+  PfCtx *c = pf_ctx_of_set(set, &which);
+  MapCtx *m = ready_map(self->map, true);
+  int step = (data->range_count - 1) / (self->max_beams - 1);
+  if (step < 1) step = 1;
+  LaserScanHost scan;
+  tabulate_scan(data, step, true, m->scale, &scan);
+  // code -> pz^3 with the host libm in the reference's expression order
+  const double z_hit_denom = 2 * self->sigma_hit * self->sigma_hit;
+  const double z_rand_mult = 1.0 / data->range_max;
+  std::vector<double> lut(m->dist_of_code.size() + 1);
+  for (size_t k = 0; k < lut.size(); k++)
+  {
+    const double z = k < m->dist_of_code.size() ? m->dist_of_code[k] : m->max_occ_dist;
+    double pz = 0.0;
+    pz += self->z_hit * exp(-(z * z) / z_hit_denom);
+    pz += self->z_rand * z_rand_mult;
+    lut[k] = pz * pz * pz;
+  }
+  return run_likelihood_field(c, which, m, 1, self->laser_pose.v, scan, lut, nullptr, 0,
+                              nullptr, nullptr);
+}
+
+// amcl_laser.cpp:305-494
+double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t *set)
+{
+  AMCLLaser *self = (AMCLLaser *)data->sensor;
+  int which = 0;
+  PfCtx *c = pf_ctx_of_set(set, &which);
+  MapCtx *m = ready_map(self->map, true);
+  int step = ceil((data->range_count) / static_cast<double>(self->max_beams));
+  if (step < 1) step = 1;
+  LaserScanHost scan;
+  tabulate_scan(data, step, true, m->scale, &scan);
+  const double z_hit_denom = 2 * self->sigma_hit * self->sigma_hit;
+  const double z_rand_mult = 1.0 / data->range_max;
+  const double max_dist_prob = exp(-(m->max_occ_dist * m->max_occ_dist) / z_hit_denom);
+  // code -> log(pz).  Last entry = off-map (:414-416).
+  std::vector<double> lut(m->dist_of_code.size() + 1);
+  std::vector<unsigned char> agree(((lut.size() + 1) & ~(size_t)1), 0);
+  for (size_t k = 0; k < lut.size(); k++)
+  {
+    double pz = 0.0;
+    if (k < m->dist_of_code.size())
+    {
+      const double z = m->dist_of_code[k];
+      agree[k] = z < self->beam_skip_distance ? 1 : 0;   // :419-421
+      pz += self->z_hit * exp(-(z * z) / z_hit_denom);
+    }
+    else
+      pz += self->z_hit * max_dist_prob;
+    pz += self->z_rand * z_rand_mult;
+    lut[k] = log(pz);
+  }
+  const bool do_beamskip = self->do_beamskip && set->converged;   // :342-344
+  if (!do_beamskip)
+    return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, nullptr, 0,
+                                nullptr, nullptr);
+
+  // Beam skipping (:446-489) as two device passes instead of the reference's
+  // N x B host scratch: pass 1 counts, per beam, the particles whose end point
+  // lies within beam_skip_distance of an obstacle; the host picks the beams;
+  // pass 2 integrates them.
+  const int slots = self->max_beams;
+  std::vector<int> obs_count(slots, 0), obs_mask(slots, 0);
+  for (size_t k = 0; k < scan.beam_ind.size(); k++)
+    if (scan.beam_ind[k] >= slots) AMCL_FATAL("beam index beyond max_beams");
+  run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, nullptr, slots,
+                       obs_count.data(), &agree);
+  int skipped = 0;
+  for (int b = 0; b < slots; b++)
+  {
+    if ((obs_count[b] / static_cast<double>(set->sample_count)) > self->beam_skip_threshold)
+      obs_mask[b] = 1;
+    else
+      skipped++;
+  }
+  bool error = false;
+  if (skipped >= (slots * self->beam_skip_error_threshold))
+  {
+    fprintf(stderr, "Over %f%% of the observations were not in the map - pf may have converged "
+                    "to wrong pose - integrating all observations\n",
+            (100 * self->beam_skip_error_threshold));
+    error = true;
+  }
+  if (error)
+    for (int b = 0; b < slots; b++) obs_mask[b] = 1;
+  // Readings the scan loop skipped (max range / NaN) are not integrated in
+  // either case: the reference would read stale scratch for them when `error`
+  // is set (:479-482), which has no defined value.  See DESIGN.md.
+  return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, obs_mask.data(),
+                              slots, nullptr, nullptr);
+}
+
+// amcl_laser.cpp:144-213
+double AMCLLaser::BeamModel(AMCLLaserData *data, pf_sample_set_t *set)
+{
+  AMCLLaser *self = (AMCLLaser *)data->sensor;
+  int which = 0;
+  PfCtx *c = pf_ctx_of_set(set, &which);
+  MapCtx *m = ready_map(self->map, false);
+  int step = (data->range_count - 1) / (self->max_beams - 1);
+  if (step < 1) step = 1;   // the reference would loop forever here (:171)
+  LaserScanHost scan;
+  tabulate_scan(data, step, false, m->scale, &scan);
+  double zp[6];
+  LaserAccess::params(self, zp);
+  return run_beam_model(c, which, m, self->laser_pose.v, scan, data->range_max, zp);
+}
+
+}  // namespace amcl

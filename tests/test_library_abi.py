@@ -1,0 +1,158 @@
+"""CPU-only checks of the drop-in boundary: the shared library loads without a
+GPU, exports every symbol the headers declare, and the ABI headers compile as
+C and as C++ with the reference's struct sizes."""
+import ctypes as C
+import os
+import subprocess
+import tempfile
+
+import pytest
+
+from navigation_b200 import abi, library
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+INC = os.path.join(ROOT, "include")
+
+
+@pytest.fixture(scope="module")
+def so():
+    if not os.path.exists(library.LIB_PATH):
+        library.build()
+    return C.CDLL(library.LIB_PATH)
+
+
+def test_exports_every_declared_symbol(so):
+    missing = [s for s in library.declared_symbols() if not hasattr(so, s)]
+    assert missing == []
+
+
+def test_exports_reference_cxx_symbols():
+    out = subprocess.run(["nm", "-D", "--defined-only", "-C", library.LIB_PATH],
+                         capture_output=True, text=True, check=True).stdout
+    for sym in [
+        "amcl::AMCLSensor::AMCLSensor()", "amcl::AMCLSensor::~AMCLSensor()",
+        "amcl::AMCLSensor::UpdateAction(", "amcl::AMCLSensor::InitSensor(",
+        "amcl::AMCLSensor::UpdateSensor(", "vtable for amcl::AMCLSensor",
+        "typeinfo for amcl::AMCLSensor", "amcl::AMCLOdom::AMCLOdom()",
+        "amcl::AMCLOdom::SetModelDiff(", "amcl::AMCLOdom::SetModelOmni(",
+        "amcl::AMCLOdom::SetModel(", "amcl::AMCLOdom::UpdateAction(",
+        "vtable for amcl::AMCLOdom", "amcl::AMCLLaser::AMCLLaser(unsigned long, map_t*)",
+        "amcl::AMCLLaser::~AMCLLaser()", "amcl::AMCLLaser::SetModelBeam(",
+        "amcl::AMCLLaser::SetModelLikelihoodField(", "amcl::AMCLLaser::SetModelLikelihoodFieldProb(",
+        "amcl::AMCLLaser::UpdateSensor(", "amcl::AMCLLaser::BeamModel(",
+        "amcl::AMCLLaser::LikelihoodFieldModel(", "amcl::AMCLLaser::LikelihoodFieldModelProb(",
+        "amcl::AMCLLaser::reallocTempData(", "vtable for amcl::AMCLLaser",
+    ]:
+        assert sym in out, sym
+
+
+def test_struct_sizes_without_gpu(so):
+    abi.bind(so, tables=(abi.FACADE_SYMBOLS,))
+    assert so.amcl_c_sizeof_pf() == 408
+    assert so.amcl_c_sizeof_laser() == 192
+    assert so.amcl_c_sizeof_odom() == 96
+
+
+def test_version_string(so):
+    so.amclb200_version.restype = C.c_char_p
+    assert b"sm_100a" in so.amclb200_version()
+
+
+def test_host_helpers_need_no_gpu(so):
+    """pf_vector / eigen helpers are host code and must run on a CPU-only box."""
+    abi.bind(so, tables=(abi.REFERENCE_SYMBOLS,))
+    a = abi.pf_vector_t()
+    a.v[:] = [1.0, 0.0, 0.5]
+    b = abi.pf_vector_t()
+    b.v[:] = [2.0, 3.0, 1.0]
+    c = so.pf_vector_coord_add(a, b)
+    import math
+    assert abs(c.v[0] - (2.0 + math.cos(1.0))) < 1e-15
+    assert abs(c.v[2] - 1.5) < 1e-15
+
+
+C_PROBE = r"""
+#include <math.h>
+#include "amcl/map/map.h"
+#include "amcl/pf/pf.h"
+#include "amcl/pf/pf_pdf.h"
+#include "amcl/pf/pf_kdtree.h"
+#include "amcl/pf/pf_vector.h"
+#include "amcl/pf/eig3.h"
+_Static_assert(sizeof(pf_t) == 408, "pf_t");
+_Static_assert(sizeof(pf_sample_set_t) == 152, "set");
+_Static_assert(sizeof(pf_sample_t) == 32, "sample");
+_Static_assert(sizeof(pf_cluster_t) == 176, "cluster");
+_Static_assert(sizeof(pf_kdtree_node_t) == 72, "node");
+_Static_assert(sizeof(map_t) == 48, "map");
+_Static_assert(sizeof(map_cell_t) == 16, "cell");
+int probe(map_t *map) { return MAP_VALID(map, (int)MAP_GXWX(map, 0.0), 0) ? MAP_INDEX(map, 1, 2) : 0; }
+"""
+
+CXX_PROBE = r"""
+#include "amcl/map/map.h"
+#include "amcl/pf/pf.h"
+#include "amcl/sensors/amcl_odom.h"
+#include "amcl/sensors/amcl_laser.h"
+using namespace amcl;
+static_assert(sizeof(AMCLSensor) == 40, "");
+static_assert(sizeof(AMCLOdom) == 96, "");
+static_assert(sizeof(AMCLOdomData) == 72, "");
+static_assert(sizeof(AMCLLaser) == 192, "");
+static_assert(sizeof(AMCLLaserData) == 48, "");
+// what amcl_node.cpp does with these types (amcl_node.cpp:934-958, 1143-1171, 1257-1329)
+bool drive(pf_t *pf, map_t *map) {
+  AMCLOdom *odom = new AMCLOdom();
+  odom->SetModel(ODOM_MODEL_DIFF, 0.2, 0.2, 0.2, 0.2, 0.2);
+  AMCLLaser *laser = new AMCLLaser(30, map);
+  laser->SetModelLikelihoodField(0.95, 0.05, 0.2, 2.0);
+  AMCLLaser *copy = new AMCLLaser(*laser);
+  pf_vector_t lp = pf_vector_zero();
+  copy->SetLaserPose(lp);
+  AMCLLaserData ldata;
+  ldata.sensor = copy;
+  ldata.range_count = 2;
+  ldata.range_max = 10.0;
+  ldata.ranges = new double[2][2];
+  AMCLOdomData odata;
+  odata.pose = lp; odata.delta = lp;
+  bool ok = odom->UpdateAction(pf, (AMCLSensorData*)&odata);
+  ok = ok && copy->UpdateSensor(pf, (AMCLSensorData*)&ldata);
+  pf->pop_err = 0.01; pf->pop_z = 0.99;
+  return ok && pf->sets[pf->current_set].samples[0].pose.v[0] == 0.0;
+}
+"""
+
+
+def _compile(src, lang, flags):
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "probe." + ("c" if lang == "c" else "cpp"))
+        with open(path, "w") as f:
+            f.write(src)
+        cc = "gcc" if lang == "c" else "g++"
+        out = subprocess.run([cc, "-c", path, "-o", os.path.join(d, "probe.o"), "-I" + INC] + flags,
+                             capture_output=True, text=True)
+        assert out.returncode == 0, out.stderr
+
+
+def test_headers_compile_as_c():
+    _compile(C_PROBE, "c", ["-std=c11", "-Wall", "-Werror"])
+
+
+def test_headers_compile_as_cxx_with_node_usage():
+    _compile(CXX_PROBE, "cxx", ["-std=c++11", "-Wall"])
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/amcl/include/amcl/pf/pf.h"),
+                    reason="reference tree not mounted")
+def test_same_probes_compile_against_reference_headers():
+    """Source compatibility: identical caller code builds against both header sets."""
+    ref_inc = ["-I/root/reference/amcl/include", "-I/root/reference/amcl/src/include"]
+    for src, lang, flags in ((CXX_PROBE, "cxx", ["-std=c++11"]),):
+        with tempfile.TemporaryDirectory() as d:
+            path = os.path.join(d, "probe.cpp")
+            with open(path, "w") as f:
+                f.write(src)
+            out = subprocess.run(["g++", "-c", path, "-o", os.path.join(d, "p.o")] + ref_inc + flags,
+                                 capture_output=True, text=True)
+            assert out.returncode == 0, out.stderr
