@@ -31,7 +31,25 @@
     abort();                                                                   \
   } while (0)
 
-#define AMCL_LAUNCH_CHECK() AMCL_CUDA(cudaGetLastError())
+// After every kernel launch.  With AMCLB200_DEBUG_SYNC=1 in the environment the
+// launch is also waited for, so a device fault is reported at the kernel that
+// raised it rather than at the next blocking call.
+inline bool amcl_debug_sync()
+{
+  static int flag = -1;
+  if (flag < 0)
+  {
+    const char *e = getenv("AMCLB200_DEBUG_SYNC");
+    flag = (e && e[0] == '1') ? 1 : 0;
+  }
+  return flag == 1;
+}
+#define AMCL_LAUNCH_CHECK()                                \
+  do                                                       \
+  {                                                        \
+    AMCL_CUDA(cudaGetLastError());                         \
+    if (amcl_debug_sync()) AMCL_CUDA(cudaDeviceSynchronize()); \
+  } while (0)
 
 namespace amclb200
 {

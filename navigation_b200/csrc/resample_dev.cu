@@ -456,16 +456,40 @@ __global__ void cc_link(HashSlot *table, unsigned int mask, const unsigned int *
   }
 }
 
-// root of every occupied bin; the smallest first-sample index per component
-__global__ void cc_roots(HashSlot *table, const unsigned int *__restrict__ slot_of,
-                         const unsigned int *__restrict__ flag, int n_valid, unsigned int *cmin)
+// Read-only find: no path halving, so it can run while nothing else writes.
+__device__ __forceinline__ unsigned int uf_find_ro(const HashSlot *t, unsigned int x)
+{
+  unsigned int p = __ldcg(&t[x].aux);
+  while (p != x)
+  {
+    x = p;
+    p = __ldcg(&t[x].aux);
+  }
+  return x;
+}
+
+// Root of every occupied bin and the smallest first-sample index per
+// component.  The root goes to a side array first: writing it into aux here
+// would race with other threads still walking the parent chains.
+__global__ void cc_roots(const HashSlot *__restrict__ table, const unsigned int *__restrict__ slot_of,
+                         const unsigned int *__restrict__ flag, int n_valid, unsigned int *cmin,
+                         unsigned int *root_of_first)
 {
   const int m = blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= n_valid || !flag[m]) return;
-  const unsigned int s = slot_of[m];
-  const unsigned int r = uf_find(table, s);
-  table[s].aux = r;
+  const unsigned int r = uf_find_ro(table, slot_of[m]);
+  root_of_first[m] = r;
   atomicMin(&cmin[r], (unsigned int)m);
+}
+
+// every occupied bin now points straight at its root
+__global__ void cc_flatten(HashSlot *table, const unsigned int *__restrict__ slot_of,
+                           const unsigned int *__restrict__ flag, int n_valid,
+                           const unsigned int *__restrict__ root_of_first)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_valid || !flag[m]) return;
+  table[slot_of[m]].aux = root_of_first[m];
 }
 
 // a sample opens a new cluster when it is the earliest sample of its component
@@ -729,7 +753,10 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
   AMCL_LAUNCH_CHECK();
   cc_link<<<nb, 256, 0, st>>>(c->d_hash, c->hash_cap - 1, c->d_slot, c->d_flag, n);
   AMCL_LAUNCH_CHECK();
-  cc_roots<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin);
+  unsigned int *root_tmp = reinterpret_cast<unsigned int *>(c->d_label);  // labels come later
+  cc_roots<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin, root_tmp);
+  AMCL_LAUNCH_CHECK();
+  cc_flatten<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, root_tmp);
   AMCL_LAUNCH_CHECK();
   // cluster-opening flags reuse d_keys' storage as u32 scratch (keys are spent)
   unsigned int *cflag = reinterpret_cast<unsigned int *>(c->d_keys);

@@ -179,17 +179,13 @@ def make_scan(lib_side, pose, n_beams, range_max=30.0, perturb=None):
 
 
 def match_clusters(a, b):
-    """Pair clusters of two tables by nearest mean; returns list of (ia, ib)."""
-    used = set()
+    """Pair clusters of two tables (different label numbering) by nearest
+    (mean x, mean y, mean heading, weight); asserts the pairing is a bijection."""
+    assert len(a) == len(b)
     pairs = []
-    for ia, (_, ma, _) in enumerate(a):
-        best, bj = None, -1
-        for ib, (_, mb, _) in enumerate(b):
-            if ib in used:
-                continue
-            d = float(np.sum((ma[:2] - mb[:2]) ** 2))
-            if best is None or d < best:
-                best, bj = d, ib
-        used.add(bj)
-        pairs.append((ia, bj))
+    for ia, (wa, ma, _) in enumerate(a):
+        d = [float(np.sum((ma[:2] - mb[:2]) ** 2) + (wa - wb) ** 2 +
+                   abs(np.angle(np.exp(1j * (ma[2] - mb[2])))) ** 2) for (wb, mb, _) in b]
+        pairs.append((ia, int(np.argmin(d))))
+    assert len(set(p[1] for p in pairs)) == len(b), "cluster tables do not pair up one-to-one"
     return pairs
