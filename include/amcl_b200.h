@@ -117,6 +117,21 @@ void amclb200_pf_last_timings(pf_t *pf, float out_ms[3]);
 void amclb200_map_calc_ranges(map_t *map, const double *rays_xya, int n, double max_range,
                               double *out_ranges);
 
+/* Device-to-device load of n particles (32-byte records) into the current set;
+ * sample_count becomes n.  For benchmarks that restart each step from one cloud. */
+void amclb200_pf_load_device(pf_t *pf, const void *d_particles, int n);
+
+/* Kernels launched by this library so far (all filters). */
+unsigned long long amclb200_launch_count(void);
+
+/* out[0] = milliseconds of the laser-model kernel of the last UpdateSensor,
+ * out[1] = particle-beam evaluations it performed. */
+void amclb200_pf_sensor_kernel_stats(pf_t *pf, double out[2]);
+
+/* Measured rate (gathers/s) of uncorrelated 2-byte gathers over a table of
+ * `table_bytes`: the L2-gather roofline of the laser kernels. */
+double amclb200_measure_gather_rate(unsigned long long table_bytes, int reps);
+
 #ifdef __cplusplus
 }
 #endif

@@ -34,6 +34,11 @@
 // After every kernel launch.  With AMCLB200_DEBUG_SYNC=1 in the environment the
 // launch is also waited for, so a device fault is reported at the kernel that
 // raised it rather than at the next blocking call.
+inline unsigned long long &amcl_launch_counter()
+{
+  static unsigned long long n = 0;
+  return n;
+}
 inline bool amcl_debug_sync()
 {
   static int flag = -1;
@@ -48,6 +53,7 @@ inline bool amcl_debug_sync()
   do                                                       \
   {                                                        \
     AMCL_CUDA(cudaGetLastError());                         \
+    amcl_launch_counter()++;                               \
     if (amcl_debug_sync()) AMCL_CUDA(cudaDeviceSynchronize()); \
   } while (0)
 

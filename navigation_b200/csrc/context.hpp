@@ -136,6 +136,9 @@ struct PfCtx
 
   // last-call timings (ms, CUDA events), for bench/diagnostics
   float ms_action = 0, ms_sensor = 0, ms_resample = 0;
+  float ms_sensor_kernel = 0;     // the laser-model kernel alone
+  long long sensor_evals = 0;     // particle-beam evaluations of that launch
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr;
 };
 
 PfCtx *pf_ctx(pf_t *pf);                       // aborts if unknown

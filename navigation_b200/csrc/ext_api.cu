@@ -95,3 +95,94 @@ void amclb200_map_calc_ranges(map_t *map, const double *rays_xya, int n, double 
 }
 
 }  // extern "C"
+
+// ---- measurement helpers --------------------------------------------------------
+
+// Uncorrelated 2-byte gathers over a table of `table_bytes`: every lane of every
+// warp reads an independent pseudo-random element, so each gather costs one
+// 32-byte L2 sector and nothing coalesces.  This is the roofline the laser
+// kernels are held against ("measured random-gather peak").
+__global__ void gather_probe_kernel(const uint16_t *__restrict__ table, unsigned int mask,
+                                    int per_thread, unsigned int *sink)
+{
+  unsigned int x = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
+  unsigned int acc = 0;
+  for (int k = 0; k < per_thread; k += 8)
+  {
+    unsigned int idx[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++)
+    {
+      x ^= x << 13; x ^= x >> 17; x ^= x << 5;   // xorshift32
+      idx[u] = x & mask;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; u++) acc += __ldg(table + idx[u]);
+  }
+  if (acc == 0xFFFFFFFFu) *sink = acc;   // keeps the loads alive
+}
+
+extern "C" {
+
+// Copies n particles from a DEVICE array (32-byte records) into the current set
+// and makes n its sample_count: lets a benchmark restart every step from the
+// same cloud without touching the host.
+void amclb200_pf_load_device(pf_t *pf, const void *d_particles, int n)
+{
+  PfCtx *c = pf_ctx(pf);
+  if (n < 0 || n > c->max_samples) AMCL_FATAL("amclb200_pf_load_device: n = %d", n);
+  const int which = pf->current_set;
+  AMCL_CUDA(cudaMemcpyAsync(c->d_set[which], d_particles, sizeof(Particle) * (size_t)n,
+                            cudaMemcpyDeviceToDevice, globals().stream));
+  pf->sets[which].sample_count = n;
+  c->host_fresh[which] = false;
+}
+
+unsigned long long amclb200_launch_count(void) { return amcl_launch_counter(); }
+
+// out[0] = laser-model kernel ms of the last UpdateSensor, out[1] = its
+// particle-beam evaluation count
+void amclb200_pf_sensor_kernel_stats(pf_t *pf, double out[2])
+{
+  PfCtx *c = pf_ctx(pf);
+  out[0] = (double)c->ms_sensor_kernel;
+  out[1] = (double)c->sensor_evals;
+}
+
+// Random 2-byte gathers per second over a table of the given footprint.
+double amclb200_measure_gather_rate(unsigned long long table_bytes, int reps)
+{
+  ensure_device();
+  unsigned int elems = 1;
+  while ((unsigned long long)elems * 2 * 2 <= table_bytes) elems <<= 1;
+  uint16_t *d_table = nullptr;
+  unsigned int *d_sink = nullptr;
+  AMCL_CUDA(cudaMalloc(&d_table, (size_t)elems * 2));
+  AMCL_CUDA(cudaMalloc(&d_sink, 4));
+  AMCL_CUDA(cudaMemset(d_table, 1, (size_t)elems * 2));
+  const int threads = 256, blocks = globals().sm_count * 8 * 4, per_thread = 256;
+  cudaEvent_t a, b;
+  AMCL_CUDA(cudaEventCreate(&a));
+  AMCL_CUDA(cudaEventCreate(&b));
+  cudaStream_t st = globals().stream;
+  gather_probe_kernel<<<blocks, threads, 0, st>>>(d_table, elems - 1, per_thread, d_sink);  // warm
+  float best = 1e30f;
+  for (int r = 0; r < reps; r++)
+  {
+    AMCL_CUDA(cudaEventRecord(a, st));
+    gather_probe_kernel<<<blocks, threads, 0, st>>>(d_table, elems - 1, per_thread, d_sink);
+    AMCL_CUDA(cudaEventRecord(b, st));
+    AMCL_CUDA(cudaEventSynchronize(b));
+    float ms = 0;
+    AMCL_CUDA(cudaEventElapsedTime(&ms, a, b));
+    if (ms < best) best = ms;
+  }
+  AMCL_CUDA(cudaGetLastError());
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  cudaFree(d_table);
+  cudaFree(d_sink);
+  return (double)blocks * threads * per_thread / (best * 1e-3);
+}
+
+}  // extern "C"

@@ -504,6 +504,12 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   const size_t smem = beam_bytes + (lut_smem ? lut_bytes : 0) + (count_mode ? sizeof(int) * (size_t)(nb + 1) : 0);
 
   int grid;
+  if (!c->ev_a)
+  {
+    AMCL_CUDA(cudaEventCreate(&c->ev_a));
+    AMCL_CUDA(cudaEventCreate(&c->ev_b));
+  }
+  AMCL_CUDA(cudaEventRecord(c->ev_a, st));
 #define AMCL_LF_LAUNCH(MODE, INSMEM)                                                     \
   do                                                                                     \
   {                                                                                      \
@@ -529,6 +535,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   }
 #undef AMCL_LF_LAUNCH
   AMCL_LAUNCH_CHECK();
+  AMCL_CUDA(cudaEventRecord(c->ev_b, st));
 
   if (count_mode)
   {
@@ -542,6 +549,8 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   finish_partials<<<1, 256, 0, st>>>(c->d_partials, grid, c->d_scalars, 0);
   AMCL_LAUNCH_CHECK();
   const double total = read_scalar(c, 0);  // also orders the staging vectors' lifetime
+  AMCL_CUDA(cudaEventElapsedTime(&c->ms_sensor_kernel, c->ev_a, c->ev_b));
+  c->sensor_evals = (long long)n * nb;
   c->host_fresh[which] = false;
   return total;
 }

@@ -31,6 +31,10 @@ EXTENSION_SYMBOLS = {
     "amclb200_pf_cumulative_table": (C.c_int, [abi.pf_p, C.c_void_p, C.c_int]),
     "amclb200_pf_last_timings": (None, [abi.pf_p, C.POINTER(C.c_float)]),
     "amclb200_map_calc_ranges": (None, [abi.map_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p]),
+    "amclb200_pf_load_device": (None, [abi.pf_p, C.c_void_p, C.c_int]),
+    "amclb200_launch_count": (C.c_uint64, []),
+    "amclb200_pf_sensor_kernel_stats": (None, [abi.pf_p, C.POINTER(C.c_double)]),
+    "amclb200_measure_gather_rate": (C.c_double, [C.c_uint64, C.c_int]),
 }
 
 RNG_PHILOX, RNG_DRAND48 = 0, 1
