@@ -132,6 +132,25 @@ void amclb200_pf_sensor_kernel_stats(pf_t *pf, double out[2]);
  * `table_bytes`: the L2-gather roofline of the laser kernels. */
 double amclb200_measure_gather_rate(unsigned long long table_bytes, int reps);
 
+/* Distance transform for callers that must not allocate device memory (a
+ * real-time loop or certified runtime with a no-allocation-after-start-up rule,
+ * or a process whose device memory belongs entirely to another allocator).
+ * It has no counterpart in the reference.  The caller owns both buffers:
+ * d_occ holds size_x*size_y occupancy states (-1 / 0 / +1, x fastest) and
+ * d_codes receives, row-major, the squared distance in cells to the nearest
+ * occupied cell, or cell_radius^2 + 1 where that exceeds cell_radius^2
+ * (occ_dist = sqrt(code)*scale, resp. max_occ_dist).  The only scratch is a
+ * fixed 4 MiB array inside the library, held by every GPU that loads it, so:
+ * at most amclb200_edt_static_max_cells() = 4 Mi cells and radius <= 254, else
+ * -2 is returned and nothing is written; calls that overlap on one GPU race on
+ * that array (serialise them); the first call on each GPU resolves the array's
+ * address and should happen at start-up, before any stream capture.  No
+ * cudaMalloc / cudaFree or other allocating call is made.  Returns 0, or
+ * -1 bad argument, -2 over the limit, -3 CUDA error. */
+int amclb200_edt_codes_static(const signed char *d_occ, int size_x, int size_y, int cell_radius,
+                              unsigned short *d_codes, void *cuda_stream);
+unsigned long long amclb200_edt_static_max_cells(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,6 +35,8 @@ EXTENSION_SYMBOLS = {
     "amclb200_launch_count": (C.c_uint64, []),
     "amclb200_pf_sensor_kernel_stats": (None, [abi.pf_p, C.POINTER(C.c_double)]),
     "amclb200_measure_gather_rate": (C.c_double, [C.c_uint64, C.c_int]),
+    "amclb200_edt_codes_static": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "amclb200_edt_static_max_cells": (C.c_uint64, []),
 }
 
 RNG_PHILOX, RNG_DRAND48 = 0, 1
