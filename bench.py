@@ -275,16 +275,12 @@ def b200_arm(args):
         lib.amcl_c_laser_update_sensor(side.laser, side.pf, scan_host.data_ptr(), args.beams, RANGE_MAX)
         lib.pf_update_resample(side.pf)
         # what the node does next (amcl_node.cpp:1369-1394): arg-max weight cluster
-        best_w, best = -1.0, None
-        w = C.c_double()
-        m = abi.pf_vector_t()
-        cv = abi.pf_matrix_t()
-        k = 0
-        while lib.pf_get_cluster_stats(side.pf, k, C.byref(w), C.byref(m), C.byref(cv)):
-            if w.value > best_w:
-                best_w, best = w.value, (m.v[0], m.v[1], m.v[2])
-            k += 1
-        return best, k
+        best = lib.amclb200_pf_best_cluster(side.pf, C.byref(bw), C.byref(bm), C.byref(bc))
+        return (best, bw.value, bm.v[0], bm.v[1], bm.v[2]), side.cur.cluster_count
+
+    bw = C.c_double()
+    bm = abi.pf_vector_t()
+    bc = abi.pf_matrix_t()
 
     def barrier():
         if world > 1:

@@ -121,8 +121,18 @@ void amclb200_map_calc_ranges(map_t *map, const double *rays_xya, int n, double 
  * sample_count becomes n.  For benchmarks that restart each step from one cloud. */
 void amclb200_pf_load_device(pf_t *pf, const void *d_particles, int n);
 
+/* The hypothesis amcl_node publishes (amcl_node.cpp:1369-1394): label, weight,
+ * mean and covariance of the heaviest cluster of the current set; -1 if none. */
+int amclb200_pf_best_cluster(pf_t *pf, double *weight, pf_vector_t *mean, pf_matrix_t *cov);
+
 /* Kernels launched by this library so far (all filters). */
 unsigned long long amclb200_launch_count(void);
+
+/* Exact cumulative table: number of times the tile-parallel form failed its
+ * recurrence check and the single-thread walk was used instead (expected 0);
+ * and a switch to force the single-thread walk (on = 0). */
+unsigned long long amclb200_cumsum_fallbacks(void);
+void amclb200_set_parallel_cumsum(int on);
 
 /* out[0] = milliseconds of the laser-model kernel of the last UpdateSensor,
  * out[1] = particle-beam evaluations it performed. */

@@ -35,7 +35,7 @@ struct Globals
   uint64_t philox_seed = 0x243F6A8885A308D3ull;
   int sm_count = 0;
   int device = -1;
-  bool exact_cumsum_parallel = false;  // tile-classified exact scan vs 1-thread walk
+  bool exact_cumsum_parallel = true;  // tile-classified exact scan vs 1-thread walk
 };
 Globals &globals();
 void ensure_device();           // fills sm_count/device once; aborts without a GPU
@@ -185,6 +185,7 @@ void run_philox_gaussian_init(PfCtx *c, int which, const double mean[3],
 
 // exact sequential-order cumulative table (pf.c:399-402) of the weights of a set
 void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum);
+unsigned long long exact_cumsum_fallback_count();
 
 struct StageTimer
 {

@@ -1,11 +1,384 @@
-// cumsum_dev.cu -- placeholder until the tile-parallel exact scan lands.
+// cumsum_dev.cu -- the cumulative weight table of pf_update_resample
+// (/root/reference/amcl/src/amcl/pf/pf.c:399-402), computed in parallel but
+// BIT-IDENTICAL to the reference's sequential  c[i+1] = fl(c[i] + w[i]).
+//
+// Why it matters: a draw r picks the index i with
+// c[i] <= r < c[i+1].  A parallel fp64 scan rounds differently from the
+// sequential sum, so at 16 M particles ~100 draws per resample would land on a
+// neighbouring particle.  "Resampled indices bit-exact" needs the exact table.
+//
+// How.  While the running sum stays inside one binade [2^e, 2^(e+1)) it is an
+// integer multiple C of u = 2^(e-52), and adding w rounds to
+//     C' = C + W + (f > 1/2) ,   w/u = W + f ,
+// with the tie f == 1/2 going to the even neighbour, i.e. depending on the
+// parity of C + W.  So every element is a function "C -> C + A[parity of C]"
+// described by a pair (A[0], A[1]), and such functions compose associatively:
+//     (g then f)[p] = g[p] + f[(p + g[p]) & 1].
+// Integer pair functions can be scanned in parallel with no rounding at all.
+//
+// The only places where this breaks are the crossings from one binade into the
+// next (a few dozen per table).  The table is cut into tiles of 1024 weights;
+// a rough fp64 prefix of the tile sums, widened by a rigorous error margin,
+// tells which tiles certainly lie inside one binade ("clean") and which might
+// contain a crossing ("dirty", typically ~20 of 16 K tiles, always including
+// tile 0).  Clean tiles go through the integer scan; dirty tiles are walked
+// element by element with real fp64 additions by one thread.  Finally EVERY
+// entry is checked against the defining recurrence c[i+1] == fl(c[i] + w[i]);
+// by induction that proves the whole table equals the sequential one.  Should
+// the check ever fail (it cannot, unless the margin reasoning is violated by
+// non-finite or negative weights) the single-thread walk is used instead.
+#include <math.h>
+
 #include "context.hpp"
 
 namespace amclb200
 {
+
+void launch_cumsum_sequential(const Particle *set, int n, double *d_cum);   // resample_dev.cu
+
+namespace
+{
+
+constexpr int kTileLen = 1024;
+constexpr int kTileThreads = 256;
+constexpr int kPerThread = kTileLen / kTileThreads;   // 4 consecutive weights per thread
+constexpr int kDirty = -100000;
+
+struct PairFn
+{
+  unsigned long long a0, a1;   // increment when the incoming C is even / odd
+};
+
+__device__ __forceinline__ PairFn fn_identity()
+{
+  PairFn r;
+  r.a0 = 0ull;
+  r.a1 = 0ull;
+  return r;
+}
+
+// g is applied first, f second.
+__device__ __forceinline__ PairFn fn_compose(const PairFn &g, const PairFn &f)
+{
+  PairFn r;
+  r.a0 = g.a0 + ((g.a0 & 1ull) ? f.a1 : f.a0);
+  r.a1 = g.a1 + (((1ull + g.a1) & 1ull) ? f.a1 : f.a0);
+  return r;
+}
+
+__device__ __forceinline__ unsigned long long fn_apply(const PairFn &f, unsigned long long C)
+{
+  return C + ((C & 1ull) ? f.a1 : f.a0);
+}
+
+// The function of one weight inside binade e (shift = 52 - e).
+__device__ __forceinline__ PairFn fn_of_weight(double w, int shift)
+{
+  const double q = scalbn(w, shift);                 // exact: power-of-two scaling
+  const unsigned long long W = (unsigned long long)q;   // q >= 0: truncation == floor
+  const double frac = q - (double)W;                 // exact
+  PairFn r;
+  if (frac > 0.5) { r.a0 = W + 1ull; r.a1 = W + 1ull; }
+  else if (frac < 0.5) { r.a0 = W; r.a1 = W; }
+  else { r.a0 = W + (W & 1ull); r.a1 = W + ((W + 1ull) & 1ull); }   // tie -> even
+  return r;
+}
+
+__device__ __forceinline__ PairFn fn_shfl_up(const PairFn &v, int delta)
+{
+  PairFn r;
+  r.a0 = __shfl_up_sync(kFullMask, v.a0, delta);
+  r.a1 = __shfl_up_sync(kFullMask, v.a1, delta);
+  return r;
+}
+
+// Block-wide exclusive scan (in thread order) under fn_compose.  s_warp needs
+// 33 entries.  Returns the exclusive prefix; *total = composition of all.
+__device__ PairFn block_scan_fn(PairFn v, PairFn *total, PairFn *s_warp)
+{
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int nw = blockDim.x >> 5;
+  PairFn inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1)
+  {
+    PairFn t = fn_shfl_up(inc, o);
+    if (lane >= o) inc = fn_compose(t, inc);
+  }
+  __syncthreads();            // protects s_warp against a previous use
+  if (lane == 31) s_warp[wid] = inc;
+  __syncthreads();
+  if (wid == 0)
+  {
+    PairFn w = lane < nw ? s_warp[lane] : fn_identity();
+    PairFn winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+      PairFn t = fn_shfl_up(winc, o);
+      if (lane >= o) winc = fn_compose(t, winc);
+    }
+    PairFn wex = fn_shfl_up(winc, 1);
+    if (lane == 0) wex = fn_identity();
+    s_warp[lane] = wex;                       // exclusive warp prefixes
+    if (lane == 31) s_warp[32] = winc;        // everything
+  }
+  __syncthreads();
+  *total = s_warp[32];
+  PairFn ex = fn_shfl_up(inc, 1);
+  if (lane == 0) ex = fn_identity();
+  return fn_compose(s_warp[wid], ex);
+}
+
+// ---- A: fp64 sum of each tile (any fixed order; only used for classification)
+__global__ void cs_tile_sums(const Particle *__restrict__ set, int n, double *__restrict__ tile_sum)
+{
+  __shared__ double s_red[32];
+  const int base = blockIdx.x * kTileLen;
+  double v = 0.0;
+#pragma unroll
+  for (int k = 0; k < kPerThread; k++)
+  {
+    const int i = base + k * kTileThreads + threadIdx.x;
+    if (i < n) v += set[i].w;
+  }
+  const double t = block_sum(v, s_red);
+  if (threadIdx.x == 0) tile_sum[blockIdx.x] = t;
+}
+
+// ---- B: rough prefix of the tile sums and clean/dirty classification ---------
+__global__ void cs_classify(const double *__restrict__ tile_sum, int tiles, int n,
+                            int *__restrict__ tile_class)
+{
+  __shared__ double s_part[1024];
+  __shared__ double s_total;
+  // pass 1: grand total (each thread a contiguous slab, then a serial combine)
+  const int per = (tiles + blockDim.x - 1) / blockDim.x;
+  const int lo = threadIdx.x * per, hi = min(tiles, lo + per);
+  double acc = 0.0;
+  for (int t = lo; t < hi; t++) acc += tile_sum[t];
+  s_part[threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+    double run = 0.0;
+    for (int k = 0; k < (int)blockDim.x; k++)
+    {
+      const double v = s_part[k];
+      s_part[k] = run;            // exclusive prefix of the slabs
+      run += v;
+    }
+    s_total = run;
+  }
+  __syncthreads();
+  // |sequential c - any fp64 prefix| <= n * 2^-53 * total for each of the two;
+  // the margin doubles that again.
+  const double total = s_total;
+  const double delta = 4.0 * (double)n * 1.1102230246251565e-16 * total;
+  double run = s_part[threadIdx.x];
+  for (int t = lo; t < hi; t++)
+  {
+    const double start = run - delta;
+    run += tile_sum[t];
+    const double end = run + delta;
+    int cls = kDirty;
+    if (start > 0.0 && isfinite(end))
+    {
+      const int e0 = ilogb(start), e1 = ilogb(end);
+      if (e0 == e1 && e0 > -900 && e0 < 900) cls = e0;
+    }
+    tile_class[t] = cls;
+  }
+}
+
+// ---- C: composed function of every clean tile ----------------------------------
+__global__ void cs_tile_fns(const Particle *__restrict__ set, int n, const int *__restrict__ tile_class,
+                            PairFn *__restrict__ tile_fn)
+{
+  __shared__ PairFn s_warp[33];
+  const int cls = tile_class[blockIdx.x];
+  if (cls == kDirty) return;                     // uniform across the block
+  const int shift = 52 - cls;
+  const int first = blockIdx.x * kTileLen + threadIdx.x * kPerThread;
+  PairFn f = fn_identity();
+#pragma unroll
+  for (int k = 0; k < kPerThread; k++)
+  {
+    const int i = first + k;
+    if (i < n) f = fn_compose(f, fn_of_weight(set[i].w, shift));
+  }
+  PairFn total;
+  block_scan_fn(f, &total, s_warp);
+  if (threadIdx.x == 0) tile_fn[blockIdx.x] = total;
+}
+
+// ---- D: exact carry into every tile; dirty tiles are walked here ---------------
+__global__ void cs_carries(const Particle *__restrict__ set, int n, int tiles,
+                           const int *__restrict__ tile_class, const PairFn *__restrict__ tile_fn,
+                           double *__restrict__ carry_in, double *__restrict__ cum)
+{
+  __shared__ PairFn s_warp[33];
+  __shared__ double s_w[kTileLen];
+  __shared__ double s_carry;
+  __shared__ int s_min[32];
+  __shared__ int s_first_dirty, s_run_class;
+  const int tid = threadIdx.x;
+  if (tid == 0)
+  {
+    s_carry = 0.0;
+    cum[0] = 0.0;
+  }
+  __syncthreads();
+  for (int base = 0; base < tiles; base += blockDim.x)
+  {
+    const int t = base + tid;
+    const bool live = t < tiles;
+    const int cls = live ? tile_class[t] : 0;
+    const bool dirty = live && cls == kDirty;
+    int cursor = 0;
+    for (;;)
+    {
+      // first dirty tile at or after the cursor (block-wide minimum)
+      int cand = (dirty && tid >= cursor) ? tid : (int)blockDim.x;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) cand = min(cand, __shfl_xor_sync(kFullMask, cand, o));
+      if ((tid & 31) == 0) s_min[tid >> 5] = cand;
+      __syncthreads();
+      if (tid < 32)
+      {
+        int v = tid < (int)(blockDim.x >> 5) ? s_min[tid] : (int)blockDim.x;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(kFullMask, v, o));
+        if (tid == 0) s_first_dirty = v;
+      }
+      if (tid == cursor) s_run_class = cls;
+      __syncthreads();
+      const int d = s_first_dirty;
+      const int run_end = min(d, tiles - base);          // clean tiles [cursor, run_end)
+      if (run_end > cursor)
+      {
+        const int e = s_run_class;
+        const bool in_run = tid >= cursor && tid < run_end;
+        PairFn f = in_run ? tile_fn[t] : fn_identity();
+        PairFn total;
+        const PairFn ex = block_scan_fn(f, &total, s_warp);
+        const unsigned long long C0 = (unsigned long long)scalbn(s_carry, 52 - e);
+        if (in_run) carry_in[t] = scalbn((double)fn_apply(ex, C0), e - 52);
+        __syncthreads();                                  // everyone has read s_carry
+        if (tid == 0) s_carry = scalbn((double)fn_apply(total, C0), e - 52);
+        __syncthreads();
+      }
+      if (d >= (int)blockDim.x || base + d >= tiles) break;
+      // walk the dirty tile with real fp64 additions
+      const int tt = base + d;
+      const int a = tt * kTileLen;
+      const int m = min(kTileLen, n - a);
+      for (int k = tid; k < m; k += blockDim.x) s_w[k] = set[a + k].w;
+      __syncthreads();
+      if (tid == 0)
+      {
+        double run = s_carry;
+        for (int k = 0; k < m; k++)
+        {
+          run = __dadd_rn(run, s_w[k]);
+          s_w[k] = run;
+        }
+        s_carry = run;
+      }
+      __syncthreads();
+      for (int k = tid; k < m; k += blockDim.x) cum[a + k + 1] = s_w[k];
+      cursor = d + 1;
+      __syncthreads();
+    }
+    __syncthreads();
+  }
+}
+
+// ---- E: per-element table of the clean tiles ----------------------------------------
+__global__ void cs_apply(const Particle *__restrict__ set, int n, const int *__restrict__ tile_class,
+                         const double *__restrict__ carry_in, double *__restrict__ cum)
+{
+  __shared__ PairFn s_warp[33];
+  const int cls = tile_class[blockIdx.x];
+  if (cls == kDirty) return;
+  const int shift = 52 - cls;
+  const int first = blockIdx.x * kTileLen + threadIdx.x * kPerThread;
+  double w[kPerThread];
+  PairFn f = fn_identity();
+#pragma unroll
+  for (int k = 0; k < kPerThread; k++)
+  {
+    const int i = first + k;
+    w[k] = i < n ? set[i].w : 0.0;
+    f = fn_compose(f, fn_of_weight(w[k], shift));
+  }
+  PairFn total;
+  const PairFn ex = block_scan_fn(f, &total, s_warp);
+  unsigned long long C = (unsigned long long)scalbn(carry_in[blockIdx.x], shift);
+  C = fn_apply(ex, C);
+#pragma unroll
+  for (int k = 0; k < kPerThread; k++)
+  {
+    const int i = first + k;
+    C = fn_apply(fn_of_weight(w[k], shift), C);
+    if (i < n) cum[i + 1] = scalbn((double)C, -shift);
+  }
+}
+
+// ---- F: the defining recurrence, checked everywhere -------------------------------------
+__global__ void cs_verify(const Particle *__restrict__ set, int n, const double *__restrict__ cum,
+                          int *bad)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double want = __dadd_rn(cum[i], set[i].w);
+  if (!(cum[i + 1] == want) || (i == 0 && cum[0] != 0.0)) *bad = 1;
+}
+
+unsigned long long g_fallbacks = 0;
+
+}  // namespace
+
+unsigned long long exact_cumsum_fallback_count() { return g_fallbacks; }
+
 void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum)
 {
-  (void)c; (void)set; (void)n; (void)d_cum;
-  AMCL_FATAL("exact_cumsum_parallel not built");
+  cudaStream_t st = globals().stream;
+  const int tiles = (n + kTileLen - 1) / kTileLen;
+  if (tiles > c->tile_cap)
+  {
+    if (c->d_tile_sum) { cudaFree(c->d_tile_sum); cudaFree(c->d_tile_carry); cudaFree(c->d_tile_fn); cudaFree(c->d_tile_class); }
+    c->tile_cap = tiles + 64;
+    AMCL_CUDA(cudaMalloc(&c->d_tile_sum, sizeof(double) * (size_t)c->tile_cap));
+    AMCL_CUDA(cudaMalloc(&c->d_tile_carry, sizeof(double) * (size_t)c->tile_cap));
+    AMCL_CUDA(cudaMalloc(&c->d_tile_fn, sizeof(PairFn) * (size_t)c->tile_cap));
+    AMCL_CUDA(cudaMalloc(&c->d_tile_class, sizeof(int) * (size_t)c->tile_cap));
+  }
+  PairFn *tile_fn = reinterpret_cast<PairFn *>(c->d_tile_fn);
+  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_sum);
+  AMCL_LAUNCH_CHECK();
+  cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, tiles, n, c->d_tile_class);
+  AMCL_LAUNCH_CHECK();
+  cs_tile_fns<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_class, tile_fn);
+  AMCL_LAUNCH_CHECK();
+  cs_carries<<<1, 1024, 0, st>>>(set, n, tiles, c->d_tile_class, tile_fn, c->d_tile_carry, d_cum);
+  AMCL_LAUNCH_CHECK();
+  cs_apply<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_class, c->d_tile_carry, d_cum);
+  AMCL_LAUNCH_CHECK();
+  const int bad_slot = 8;
+  AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, sizeof(int), st));
+  cs_verify<<<(n + 255) / 256, 256, 0, st>>>(set, n, d_cum, c->d_ints + bad_slot);
+  AMCL_LAUNCH_CHECK();
+  AMCL_CUDA(cudaMemcpyAsync(c->h_ints + bad_slot, c->d_ints + bad_slot, sizeof(int),
+                            cudaMemcpyDeviceToHost, st));
+  AMCL_CUDA(cudaStreamSynchronize(st));
+  if (c->h_ints[bad_slot])
+  {
+    g_fallbacks++;
+    fprintf(stderr, "[amcl_b200] exact_cumsum: recurrence check failed (non-finite or negative "
+                    "weights?); using the single-thread walk\n");
+    launch_cumsum_sequential(set, n, d_cum);
+  }
 }
+
 }  // namespace amclb200

@@ -138,7 +138,38 @@ void amclb200_pf_load_device(pf_t *pf, const void *d_particles, int n)
   c->host_fresh[which] = false;
 }
 
+// The node's hypothesis selection (amcl_node.cpp:1369-1394): the cluster of
+// the current set with the largest weight.  Returns its label, or -1.
+int amclb200_pf_best_cluster(pf_t *pf, double *weight, pf_vector_t *mean, pf_matrix_t *cov)
+{
+  pf_sample_set_t *set = pf->sets + pf->current_set;
+  double max_weight = 0.0;
+  int best = -1;
+  for (int k = 0; k < set->cluster_count; k++)
+  {
+    double w;
+    pf_vector_t m;
+    pf_matrix_t c;
+    if (!pf_get_cluster_stats(pf, k, &w, &m, &c)) break;
+    if (w > max_weight)
+    {
+      max_weight = w;
+      best = k;
+      *weight = w;
+      *mean = m;
+      *cov = c;
+    }
+  }
+  return best;
+}
+
 unsigned long long amclb200_launch_count(void) { return amcl_launch_counter(); }
+
+// How often the exact cumulative table had to fall back to the single-thread walk.
+unsigned long long amclb200_cumsum_fallbacks(void) { return exact_cumsum_fallback_count(); }
+
+// 1: tile-parallel exact table for large sets (default); 0: always the single-thread walk.
+void amclb200_set_parallel_cumsum(int on) { globals().exact_cumsum_parallel = on != 0; }
 
 // out[0] = laser-model kernel ms of the last UpdateSensor, out[1] = its
 // particle-beam evaluation count

@@ -236,15 +236,18 @@ __global__ void cumsum_sequential(const Particle *__restrict__ set, int n, doubl
 
 void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum);  // cumsum_dev.cu
 
-void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum)
+void launch_cumsum_sequential(const Particle *set, int n, double *d_cum)
 {
-  if (globals().exact_cumsum_parallel && n >= 32768)
-  {
-    exact_cumsum_parallel(c, set, n, d_cum);
-    return;
-  }
   cumsum_sequential<<<1, 256, 0, globals().stream>>>(set, n, d_cum);
   AMCL_LAUNCH_CHECK();
+}
+
+void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum)
+{
+  if (globals().exact_cumsum_parallel && n >= 16384)
+    exact_cumsum_parallel(c, set, n, d_cum);
+  else
+    launch_cumsum_sequential(set, n, d_cum);
 }
 
 // ------------------------------------------------------- draw + search + copy --
@@ -556,20 +559,30 @@ __global__ void cluster_accumulate(const Particle *__restrict__ set, int n,
     v[9] = s.w * s.y * s.y;
     if (label_out) label_out[i] = (int)label;
   }
-  // warp-uniform label (the converged case): one atomic per warp and value
-  const unsigned int first = __shfl_sync(kFullMask, label, 0);
-  const bool uniform = __all_sync(kFullMask, label == first);
-  if (uniform)
+  // Aggregate inside the warp before touching memory: lanes that share a label
+  // are summed with shuffles and their leader issues one atomic per value.  A
+  // converged cloud is one label per warp; a global cloud is one giant free-
+  // space component plus a few stragglers.  After four distinct labels the
+  // remaining lanes (rare) add individually.
+  const int lane = threadIdx.x & 31;
+  unsigned remaining = __ballot_sync(kFullMask, live && label != 0xFFFFFFFFu);
+  int rounds = 0;
+  while (remaining != 0u && rounds < 4)
   {
-    if (first == 0xFFFFFFFFu) return;
+    const int leader = __ffs(remaining) - 1;
+    const unsigned int lab = __shfl_sync(kFullMask, label, leader);
+    const bool mine = live && label == lab;
+    const unsigned group = __ballot_sync(kFullMask, mine);
 #pragma unroll
     for (int q = 0; q < 10; q++)
     {
-      const double t = warp_sum(v[q]);
-      if ((threadIdx.x & 31) == 0) atomicAdd(&acc[(size_t)first * 10 + q], t);
+      const double t = warp_sum(mine ? v[q] : 0.0);
+      if (lane == leader) atomicAdd(&acc[(size_t)lab * 10 + q], t);
     }
+    remaining &= ~group;
+    rounds++;
   }
-  else if (live)
+  if (live && label != 0xFFFFFFFFu && ((remaining >> lane) & 1u))
   {
 #pragma unroll
     for (int q = 0; q < 10; q++) atomicAdd(&acc[(size_t)label * 10 + q], v[q]);

@@ -337,24 +337,66 @@ def test_resample_vs_golden(lib, g, tag):
     side.close()
 
 
-def test_cumulative_table_bit_exact(lib, port):
-    """C5: the table must be the SEQUENTIAL fp64 running sum, bit for bit."""
+def _weights(kind, n, seed):
+    rng = np.random.default_rng(seed)
+    if kind == "gamma":
+        w = rng.gamma(0.5, size=n)
+        w[::97] = 0.0                       # zero-weight runs
+        w[5] = w.sum() * 0.3                # one dominant particle
+    elif kind == "uniform":
+        w = np.full(n, 1.0)
+    elif kind == "dyadic":                  # short mantissas: exact-half ties are common
+        w = np.ldexp(np.round(rng.gamma(0.5, size=n) * 64) + 1.0, -30)
+    elif kind == "tiny":                    # LFP-like: almost all weight on a few particles
+        w = np.exp(-rng.uniform(0, 700, size=n))
+        w[n // 3] = 1.0
+    elif kind == "posterior":               # what a sensor update leaves behind
+        w = (1.0 + rng.gamma(2.0, size=n) * 50.0)
+    w = w / w.sum()
+    if kind == "dyadic":
+        w = np.ldexp(np.round(np.ldexp(w, 44)), -44)
+    return w
+
+
+@pytest.mark.parametrize("kind,n,seed", [("gamma", 5000, 1), ("gamma", 70000, 2), ("uniform", 300001, 3),
+                                         ("dyadic", 200000, 4), ("tiny", 150000, 5),
+                                         ("posterior", 2500000, 6), ("gamma", 16384, 7)])
+def test_cumulative_table_bit_exact(lib, port, kind, n, seed):
+    """C5: the table must be the SEQUENTIAL fp64 running sum, bit for bit -- for
+    the single-thread walk (small n) and the tile-parallel exact scan (large n)."""
     occ = synth.rooms_map(80, seed=1, room=40, door=(10, 20))
-    for n, seed in ((5000, 1), (70000, 2), (300001, 3)):
-        side = Side(lib, occ)
-        side.alloc(10, n)
-        cloud = np.zeros((n, 4))
-        w = np.random.default_rng(seed).gamma(0.5, size=n)
-        w[:: 97] = 0.0                       # zero-weight runs
-        w[5] = w.sum() * 0.3                 # one dominant particle
-        cloud[:, 3] = w / w.sum()
-        side.set_samples(cloud)
-        got = np.empty(n + 1)
-        assert lib.amclb200_pf_cumulative_table(side.pf, got.ctypes.data, n + 1) == n + 1
-        want = np.empty(n + 1)
-        port.orc_cumsum(cloud, n, want)
-        assert np.array_equal(got, want)
-        side.close()
+    side = Side(lib, occ)
+    side.alloc(10, n)
+    cloud = np.zeros((n, 4))
+    cloud[:, 3] = _weights(kind, n, seed)
+    side.set_samples(cloud)
+    before = lib.amclb200_cumsum_fallbacks()
+    got = np.empty(n + 1)
+    assert lib.amclb200_pf_cumulative_table(side.pf, got.ctypes.data, n + 1) == n + 1
+    want = np.empty(n + 1)
+    port.orc_cumsum(cloud, n, want)
+    assert np.array_equal(got, want)
+    assert lib.amclb200_cumsum_fallbacks() == before   # the parallel form held its own check
+    side.close()
+
+
+def test_cumulative_table_survives_bad_weights(lib, port):
+    """Negative weights break the binade reasoning; the recurrence check must
+    notice and the single-thread walk must still deliver the sequential sum."""
+    occ = synth.rooms_map(80, seed=1, room=40, door=(10, 20))
+    n = 50000
+    side = Side(lib, occ)
+    side.alloc(10, n)
+    cloud = np.zeros((n, 4))
+    w = np.random.default_rng(9).normal(size=n)
+    cloud[:, 3] = w
+    side.set_samples(cloud)
+    got = np.empty(n + 1)
+    lib.amclb200_pf_cumulative_table(side.pf, got.ctypes.data, n + 1)
+    want = np.empty(n + 1)
+    port.orc_cumsum(cloud, n, want)
+    assert np.array_equal(got, want)
+    side.close()
 
 
 def test_pf_init_and_cluster_stats(lib, g):
