@@ -528,65 +528,108 @@ __global__ void cc_assign_ids(const HashSlot *__restrict__ table, const unsigned
 
 // pf.c:603-643: per sample, ten weighted sums into its cluster's accumulators
 // [count, w, w x, w y, w cos, w sin, w xx, w xy, w yx, w yy].
+//
+// Persistent warps walk the samples 32 at a time.  Each warp keeps a "hot"
+// label and every lane keeps private partial sums for it, so the common cases
+// -- a converged cloud (one cluster) or a global cloud (one giant free-space
+// component plus stragglers) -- cost ten atomics per WARP LIFETIME instead of
+// ten per sample.  Lanes on other labels are combined with shuffles (up to
+// three further labels per batch) and only then fall back to single atomics.
+__device__ __forceinline__ void flush_hot(double *acc, unsigned int hot, double h[10], int lane)
+{
+  if (hot == 0xFFFFFFFFu) return;   // warp-uniform
+#pragma unroll
+  for (int q = 0; q < 10; q++)
+  {
+    const double t = warp_sum(h[q]);
+    if (lane == 0 && t != 0.0) atomicAdd(&acc[(size_t)hot * 10 + q], t);
+    h[q] = 0.0;
+  }
+}
+
 __global__ void cluster_accumulate(const Particle *__restrict__ set, int n,
                                    const HashSlot *__restrict__ table,
                                    const unsigned int *__restrict__ slot_of,
                                    const unsigned int *__restrict__ cid_of_root, double *acc,
                                    int *label_out)
 {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool live = i < n;
-  unsigned int label = 0xFFFFFFFFu;
-  double v[10];
-#pragma unroll
-  for (int q = 0; q < 10; q++) v[q] = 0.0;
-  if (live)
-  {
-    const Particle s = load_particle(set + i);
-    const unsigned int root = table[slot_of[i]].aux;
-    label = cid_of_root[root];
-    double sn, cs;
-    sincos(s.th, &sn, &cs);
-    v[0] = 1.0;
-    v[1] = s.w;
-    v[2] = s.w * s.x;
-    v[3] = s.w * s.y;
-    v[4] = s.w * cs;
-    v[5] = s.w * sn;
-    v[6] = s.w * s.x * s.x;
-    v[7] = s.w * s.x * s.y;
-    v[8] = s.w * s.y * s.x;
-    v[9] = s.w * s.y * s.y;
-    if (label_out) label_out[i] = (int)label;
-  }
-  // Aggregate inside the warp before touching memory: lanes that share a label
-  // are summed with shuffles and their leader issues one atomic per value.  A
-  // converged cloud is one label per warp; a global cloud is one giant free-
-  // space component plus a few stragglers.  After four distinct labels the
-  // remaining lanes (rare) add individually.
   const int lane = threadIdx.x & 31;
-  unsigned remaining = __ballot_sync(kFullMask, live && label != 0xFFFFFFFFu);
-  int rounds = 0;
-  while (remaining != 0u && rounds < 4)
-  {
-    const int leader = __ffs(remaining) - 1;
-    const unsigned int lab = __shfl_sync(kFullMask, label, leader);
-    const bool mine = live && label == lab;
-    const unsigned group = __ballot_sync(kFullMask, mine);
+  const int warps_per_block = blockDim.x >> 5;
+  const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  const int warp_stride = gridDim.x * warps_per_block;
+  unsigned int hot = 0xFFFFFFFFu;
+  double h[10];
 #pragma unroll
-    for (int q = 0; q < 10; q++)
+  for (int q = 0; q < 10; q++) h[q] = 0.0;
+
+  for (long long base = (long long)warp_global * 32; base < n; base += (long long)warp_stride * 32)
+  {
+    const int i = (int)base + lane;
+    const bool live = i < n;
+    unsigned int label = 0xFFFFFFFFu;
+    double v[10];
+#pragma unroll
+    for (int q = 0; q < 10; q++) v[q] = 0.0;
+    if (live)
     {
-      const double t = warp_sum(mine ? v[q] : 0.0);
-      if (lane == leader) atomicAdd(&acc[(size_t)lab * 10 + q], t);
+      const Particle s = load_particle(set + i);
+      const unsigned int root = table[slot_of[i]].aux;
+      label = cid_of_root[root];
+      double sn, cs;
+      sincos(s.th, &sn, &cs);
+      v[0] = 1.0;
+      v[1] = s.w;
+      v[2] = s.w * s.x;
+      v[3] = s.w * s.y;
+      v[4] = s.w * cs;
+      v[5] = s.w * sn;
+      v[6] = s.w * s.x * s.x;
+      v[7] = s.w * s.x * s.y;
+      v[8] = s.w * s.y * s.x;
+      v[9] = s.w * s.y * s.y;
+      if (label_out) label_out[i] = (int)label;
     }
-    remaining &= ~group;
-    rounds++;
-  }
-  if (live && label != 0xFFFFFFFFu && ((remaining >> lane) & 1u))
-  {
+    const bool valid = live && label != 0xFFFFFFFFu;
+    unsigned remaining = __ballot_sync(kFullMask, valid);
+    if (remaining == 0u) continue;
+    unsigned hot_group = __ballot_sync(kFullMask, valid && label == hot);
+    if (hot_group == 0u)
+    {
+      // nobody here belongs to the hot cluster any more: retire it, adopt the
+      // label of the first valid lane
+      flush_hot(acc, hot, h, lane);
+      hot = __shfl_sync(kFullMask, label, __ffs(remaining) - 1);
+      hot_group = __ballot_sync(kFullMask, valid && label == hot);
+    }
+    if (valid && label == hot)
+    {
 #pragma unroll
-    for (int q = 0; q < 10; q++) atomicAdd(&acc[(size_t)label * 10 + q], v[q]);
+      for (int q = 0; q < 10; q++) h[q] += v[q];
+    }
+    remaining &= ~hot_group;
+    int rounds = 0;
+    while (remaining != 0u && rounds < 3)
+    {
+      const int leader = __ffs(remaining) - 1;
+      const unsigned int lab = __shfl_sync(kFullMask, label, leader);
+      const bool mine = valid && label == lab;
+      const unsigned group = __ballot_sync(kFullMask, mine);
+#pragma unroll
+      for (int q = 0; q < 10; q++)
+      {
+        const double t = warp_sum(mine ? v[q] : 0.0);
+        if (lane == leader) atomicAdd(&acc[(size_t)lab * 10 + q], t);
+      }
+      remaining &= ~group;
+      rounds++;
+    }
+    if (valid && ((remaining >> lane) & 1u))
+    {
+#pragma unroll
+      for (int q = 0; q < 10; q++) atomicAdd(&acc[(size_t)label * 10 + q], v[q]);
+    }
   }
+  flush_hot(acc, hot, h, lane);
 }
 
 // sum x, sum y (pf.c:231-236) -> block partials (two lanes of the partial array)
@@ -789,8 +832,12 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
     AMCL_CUDA(cudaMalloc(&c->d_cluster_acc, sizeof(double) * 10 * (size_t)c->cluster_acc_cap));
   }
   AMCL_CUDA(cudaMemsetAsync(c->d_cluster_acc, 0, sizeof(double) * 10 * (size_t)(ncl > 0 ? ncl : 1), st));
-  cluster_accumulate<<<nb, 256, 0, st>>>(c->d_set[which], n, c->d_hash, c->d_slot, cmin,
-                                         c->d_cluster_acc, c->d_label);
+  {
+    int grid = globals().sm_count * 8;
+    if (grid > nb) grid = nb;
+    cluster_accumulate<<<grid, 256, 0, st>>>(c->d_set[which], n, c->d_hash, c->d_slot, cmin,
+                                             c->d_cluster_acc, c->d_label);
+  }
   AMCL_LAUNCH_CHECK();
   std::vector<double> acc((size_t)10 * (ncl > 0 ? ncl : 1));
   AMCL_CUDA(cudaMemcpyAsync(acc.data(), c->d_cluster_acc, sizeof(double) * 10 * (size_t)ncl,
