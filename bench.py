@@ -245,12 +245,21 @@ def b200_arm(args):
     from tests.scenario import Side
 
     lib = library.load()
-    lib.amclb200_set_rng(library.RNG_PHILOX, 0x5EED + rank)
+    lib.amclb200_set_rng(library.RNG_PHILOX, 0x5EED)       # one seed: ranks share one filter
     occ, pose, bear = build_world(args.map_size, args.beams)
     side = Side(lib, occ, scale=SCALE)
     n_total = args.particles
-    n_local = n_total // world
-    side.alloc(100, n_local, pop_err=0.01, pop_z=0.99)
+    # every rank allocates the GLOBAL filter and owns a contiguous slice of it
+    side.alloc(100, n_total, pop_err=0.01, pop_z=0.99)
+    coll = None
+    if world > 1:
+        from navigation_b200 import sharded
+        coll = sharded.Collectives(device=torch.device("cuda", local))
+        coll.attach(lib, side.pf)
+    rng2 = (C.c_int * 2)()
+    lib.amclb200_pf_shard_range(side.pf, n_total, rng2)
+    own_lo, own_hi = rng2[0], rng2[1]
+    n_local = own_hi - own_lo
     lib.amclb200_set_mirror(side.pf, 0)      # deferred host mirror
     t0 = time.perf_counter()
     side.make_laser(args.beams, model="lf", **dict(LASER, max_occ_dist=MAX_OCC_DIST))  # GPU EDT
@@ -259,18 +268,16 @@ def b200_arm(args):
     scan = scan_from(side, pose, bear, gpu=True)
     used_beams = int(np.sum(scan[:, 0] < RANGE_MAX))
 
-    cloud = synth.uniform_cloud(occ, SCALE, n_local, 100 + rank)
-    pristine = torch.from_numpy(cloud).cuda()
+    # the same global cloud on every rank (hash of the global index); keep the own slice
+    cloud = synth.uniform_cloud(occ, SCALE, n_total, 100)[own_lo:own_hi]
+    pristine = torch.from_numpy(np.ascontiguousarray(cloud)).cuda()
     del cloud
     scan_host = torch.from_numpy(scan).pin_memory()
     odom_pose = (C.c_double * 3)(*ODOM_POSE)
     odom_delta = (C.c_double * 3)(*ODOM_DELTA)
 
-    if world > 1:
-        raise SystemExit("multi-GPU sharded update: see navigation_b200/sharded.py (not wired yet)")
-
     def step():
-        lib.amclb200_pf_load_device(side.pf, pristine.data_ptr(), n_local)
+        lib.amclb200_pf_load_device_shard(side.pf, pristine.data_ptr(), n_total)
         lib.amcl_c_odom_update_action(side.odom, side.pf, odom_pose, odom_delta)
         lib.amcl_c_laser_update_sensor(side.laser, side.pf, scan_host.data_ptr(), args.beams, RANGE_MAX)
         lib.pf_update_resample(side.pf)
@@ -369,6 +376,7 @@ def b200_arm(args):
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
         "roofline": roofline,
+        "collectives": (dict(coll.calls, note="counts over warm-up + timed + e2e steps; in-place NCCL via torch.distributed") if coll else None),
         "stage_ms": {"action": float(np.mean([s[0] for s in stages])),
                      "sensor": float(np.mean([s[1] for s in stages])),
                      "resample": float(np.mean([s[2] for s in stages])),

@@ -125,6 +125,27 @@ void amclb200_pf_load_device(pf_t *pf, const void *d_particles, int n);
  * mean and covariance of the heaviest cluster of the current set; -1 if none. */
 int amclb200_pf_best_cluster(pf_t *pf, double *weight, pf_vector_t *mean, pf_matrix_t *cov);
 
+/* ---- several GPUs, one process each -------------------------------------------
+ * Collectives are supplied by the host program (torch.distributed / NCCL in
+ * bench.py).  Both act IN PLACE on DEVICE buffers and must be ordered with the
+ * library's stream.  dtype: 0 = fp64, 1 = int32; op: 0 = sum, 1 = min, 2 = max.
+ * all-gather: rank r's block of bytes_per_rank bytes sits at offset
+ * r * bytes_per_rank of d_buf on entry; all blocks are present on return. */
+typedef void (*amclb200_allreduce_fn)(void *d_buf, int count, int dtype, int op, void *user);
+typedef void (*amclb200_allgather_fn)(void *d_buf, unsigned long long bytes_per_rank, void *user);
+
+/* Makes this filter rank `rank` of `world`.  Every rank allocates the filter
+ * with the same (global) max_samples and issues the same calls; each keeps only
+ * its contiguous slice of the particle arrays current and the library inserts
+ * the exchanges the algorithm needs (weight totals, the source set and the bin
+ * keys before resampling, per-cluster sums).  Results equal the one-GPU run. */
+void amclb200_pf_set_shard(pf_t *pf, int rank, int world, amclb200_allreduce_fn allreduce,
+                           amclb200_allgather_fn allgather, void *user);
+/* Device-to-device load of this rank's slice of an n_global-particle cloud. */
+void amclb200_pf_load_device_shard(pf_t *pf, const void *d_slice, int n_global);
+/* out = [lo, hi): the slice of a set of n particles this rank owns. */
+void amclb200_pf_shard_range(pf_t *pf, int n, int out[2]);
+
 /* Kernels launched by this library so far (all filters). */
 unsigned long long amclb200_launch_count(void);
 

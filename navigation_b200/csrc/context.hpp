@@ -88,17 +88,50 @@ struct HashSlot
 };
 constexpr unsigned long long kEmptyKey = ~0ull;
 
+// ---- sharding over GPUs -------------------------------------------------------------
+//
+// One process per GPU.  Every rank holds a filter sized for the WHOLE particle
+// set (arrays are indexed by the global particle index), but owns -- computes
+// and keeps current -- only the contiguous slice [rank*chunk, (rank+1)*chunk)
+// with chunk = ceil(n / world).  Steps that need another rank's data
+// (resampling draws over the global table) first all-gather the slices in
+// place.  The collectives themselves are supplied by the host program as
+// callbacks (torch.distributed over NCCL in bench.py): they act IN PLACE on
+// device buffers and are stream-ordered with the library's stream.
+typedef void (*shard_allreduce_fn)(void *d_buf, int count, int dtype, int op, void *user);
+typedef void (*shard_allgather_fn)(void *d_buf, unsigned long long bytes_per_rank, void *user);
+enum { SHARD_F64 = 0, SHARD_I32 = 1 };
+enum { SHARD_SUM = 0, SHARD_MIN = 1, SHARD_MAX = 2 };
+
+struct Shard
+{
+  int rank = 0, world = 1;
+  shard_allreduce_fn allreduce = nullptr;
+  shard_allgather_fn allgather = nullptr;
+  void *user = nullptr;
+  bool on() const { return world > 1; }
+  int chunk(int n) const { return (n + world - 1) / world; }
+  int lo(int n) const { int v = rank * chunk(n); return v < n ? v : n; }
+  int hi(int n) const { int v = (rank + 1) * chunk(n); return v < n ? v : n; }
+  int count(int n) const { return hi(n) - lo(n); }
+};
+
 struct PfCtx
 {
   pf_t *host = nullptr;
   int max_samples = 0;
+  int alloc_samples = 0;          // max_samples padded so world*chunk always fits
+  Shard shard;
+  bool replicated[2] = {true, true};  // whole set valid on this rank (not only the owned slice)
   Particle *d_set[2] = {nullptr, nullptr};
   bool mirror_eager = true;       // D2H the sample array after every update
   bool host_fresh[2] = {false, false};
 
   // resampling scratch
   double *d_cum = nullptr;        // max+1 cumulative table
-  double *d_draws = nullptr;      // 2*max uniforms (u_test, r) or 6*max (motion)
+  double *d_draws = nullptr;      // 2*max uniforms (u_test, r) of a resample
+  double *d_motion_draws = nullptr;  // parity mode: 6 doubles per particle, grown on demand
+  int motion_draws_cap = 0;
   int *d_src = nullptr;           // source index per output sample
   unsigned long long *d_keys = nullptr;
   unsigned int *d_slot = nullptr; // hash slot per sample
@@ -142,6 +175,7 @@ struct PfCtx
 };
 
 PfCtx *pf_ctx(pf_t *pf);                       // aborts if unknown
+void pf_replicate(PfCtx *c, int which);        // all-gather the owned slices if needed
 PfCtx *pf_ctx_of_set(pf_sample_set_t *set, int *which);
 PfCtx *pf_ctx_create(pf_t *pf);
 void pf_ctx_release(pf_t *pf);

@@ -163,6 +163,53 @@ int amclb200_pf_best_cluster(pf_t *pf, double *weight, pf_vector_t *mean, pf_mat
   return best;
 }
 
+// ---- sharding over GPUs (one process per GPU) --------------------------------------
+
+// Declares this filter to be rank `rank` of `world` cooperating processes that
+// all hold a filter of the same max_samples and issue the same call sequence.
+// From then on UpdateAction / UpdateSensor / pf_update_resample touch only the
+// rank's slice [rank*ceil(n/world), ...) of the particle arrays and call the
+// two host-supplied collectives (in place, on device buffers, ordered with the
+// library's stream) where the reference's algorithm needs global data.
+void amclb200_pf_set_shard(pf_t *pf, int rank, int world, shard_allreduce_fn allreduce,
+                           shard_allgather_fn allgather, void *user)
+{
+  PfCtx *c = pf_ctx(pf);
+  if (world < 1 || rank < 0 || rank >= world || world > 1024)
+    AMCL_FATAL("amclb200_pf_set_shard: rank %d of %d", rank, world);
+  if (world > 1 && (!allreduce || !allgather))
+    AMCL_FATAL("amclb200_pf_set_shard: collectives are required when world > 1");
+  c->shard.rank = rank;
+  c->shard.world = world;
+  c->shard.allreduce = allreduce;
+  c->shard.allgather = allgather;
+  c->shard.user = user;
+}
+
+// Loads THIS RANK'S slice of a cloud of n_global particles from a device array
+// holding just that slice (ceil(n_global/world) records or fewer for the last rank).
+void amclb200_pf_load_device_shard(pf_t *pf, const void *d_slice, int n_global)
+{
+  PfCtx *c = pf_ctx(pf);
+  if (n_global < 0 || n_global > c->max_samples) AMCL_FATAL("load_device_shard: n = %d", n_global);
+  const int which = pf->current_set;
+  const int lo = c->shard.lo(n_global), cnt = c->shard.count(n_global);
+  if (cnt > 0)
+    AMCL_CUDA(cudaMemcpyAsync(c->d_set[which] + lo, d_slice, sizeof(Particle) * (size_t)cnt,
+                              cudaMemcpyDeviceToDevice, globals().stream));
+  pf->sets[which].sample_count = n_global;
+  c->host_fresh[which] = false;
+  c->replicated[which] = !c->shard.on();
+}
+
+// [lo, hi) of this rank's slice for a set of n particles.
+void amclb200_pf_shard_range(pf_t *pf, int n, int out[2])
+{
+  PfCtx *c = pf_ctx(pf);
+  out[0] = c->shard.lo(n);
+  out[1] = c->shard.hi(n);
+}
+
 unsigned long long amclb200_launch_count(void) { return amcl_launch_counter(); }
 
 // How often the exact cumulative table had to fall back to the single-thread walk.

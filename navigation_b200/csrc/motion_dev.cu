@@ -34,8 +34,9 @@ struct MotionArgs
   // DIFF: rot1_n, trans, rot2_n, sd1, sd2, sd3   (rot*_n already wrapped)
   // OMNI: bearing0, trans, rot, sd_trans, sd_rot, sd_strafe
   double k[6];
-  const double *draws;       // parity: 6 doubles per particle, else null
+  const double *draws;       // parity: 6 doubles per particle (global index), else null
   uint64_t key;              // Philox key
+  int offset;                // global index of set[0] (sharded runs own a slice)
 };
 
 __device__ __forceinline__ double wrap_angle(double z) { return atan2(sin(z), cos(z)); }
@@ -59,13 +60,13 @@ __global__ void motion_kernel(const MotionArgs a)
   double g[3];
   if (a.draws)
   {
-    const double *d = a.draws + 6 * (size_t)i;
+    const double *d = a.draws + 6 * (size_t)(a.offset + i);
 #pragma unroll
     for (int q = 0; q < 3; q++) g[q] = a.k[3 + q] * d[2 * q] * d[2 * q + 1];  // sigma*x2*s
   }
   else
   {
-    PhiloxStream rng(a.key, (uint64_t)i);
+    PhiloxStream rng(a.key, (uint64_t)(a.offset + i));
 #pragma unroll
     for (int q = 0; q < 3; q++) g[q] = rng.gaussian(a.k[3 + q]);
   }
@@ -129,26 +130,35 @@ void run_motion(PfCtx *c, int which, int model, const double consts[8],
 {
   cudaStream_t st = globals().stream;
   const int n = c->host->sets[which].sample_count;
+  const int lo = c->shard.lo(n), cnt = c->shard.count(n);   // whole set when not sharded
   MotionArgs a;
-  a.set = c->d_set[which];
-  a.n = n;
+  a.set = c->d_set[which] + lo;
+  a.n = cnt;
+  a.offset = lo;
   a.model = model;
   for (int q = 0; q < 6; q++) a.k[q] = consts[q];
   a.draws = nullptr;
   if (host_draws_or_null)
   {
-    AMCL_CUDA(cudaMemcpyAsync(c->d_draws, host_draws_or_null, sizeof(double) * 6 * (size_t)n,
+    if (n > c->motion_draws_cap)
+    {
+      if (c->d_motion_draws) cudaFree(c->d_motion_draws);
+      c->motion_draws_cap = n + 1024;
+      AMCL_CUDA(cudaMalloc(&c->d_motion_draws, sizeof(double) * 6 * (size_t)c->motion_draws_cap));
+    }
+    AMCL_CUDA(cudaMemcpyAsync(c->d_motion_draws, host_draws_or_null, sizeof(double) * 6 * (size_t)n,
                               cudaMemcpyHostToDevice, st));
-    a.draws = c->d_draws;
+    a.draws = c->d_motion_draws;
   }
   a.key = globals().philox_seed ^ (0x9E3779B97F4A7C15ull * (++c->step));
-  if (n > 0)
+  if (cnt > 0)
   {
-    motion_kernel<<<(n + 127) / 128, 128, 0, st>>>(a);
+    motion_kernel<<<(cnt + 127) / 128, 128, 0, st>>>(a);
     AMCL_LAUNCH_CHECK();
   }
   if (host_draws_or_null) AMCL_CUDA(cudaStreamSynchronize(st));  // caller's buffer lifetime
   c->host_fresh[which] = false;
+  if (c->shard.on()) c->replicated[which] = false;
 }
 
 void run_philox_gaussian_init(PfCtx *c, int which, const double mean[3], const double cr[9],
@@ -166,6 +176,7 @@ void run_philox_gaussian_init(PfCtx *c, int which, const double mean[3], const d
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaStreamSynchronize(st));
   c->host_fresh[which] = false;
+  c->replicated[which] = true;   // every rank generates the whole (identical) cloud
 }
 
 }  // namespace amclb200

@@ -66,12 +66,14 @@ PfCtx *pf_ctx_create(pf_t *pf)
   ensure_device();
   PfCtx *c = new PfCtx();
   c->host = pf;
-  const size_t maxs = (size_t)pf->max_samples;
+  // arrays are padded so that world * ceil(n / world) slices always fit
+  const size_t maxs = (size_t)pf->max_samples + 1024;
   c->max_samples = pf->max_samples;
+  c->alloc_samples = (int)maxs;
   c->hash_cap = next_pow2((unsigned int)(2 * maxs + 2));
   for (int j = 0; j < 2; j++) AMCL_CUDA(cudaMalloc(&c->d_set[j], sizeof(Particle) * maxs));
   AMCL_CUDA(cudaMalloc(&c->d_cum, sizeof(double) * (maxs + 1)));
-  AMCL_CUDA(cudaMalloc(&c->d_draws, sizeof(double) * 6 * maxs));
+  AMCL_CUDA(cudaMalloc(&c->d_draws, sizeof(double) * 2 * maxs));
   AMCL_CUDA(cudaMalloc(&c->d_src, sizeof(int) * maxs));
   AMCL_CUDA(cudaMalloc(&c->d_label, sizeof(int) * maxs));
   AMCL_CUDA(cudaMalloc(&c->d_keys, sizeof(unsigned long long) * maxs));
@@ -96,6 +98,7 @@ void pf_ctx_release(pf_t *pf)
   if (it == r.end()) return;
   PfCtx *c = it->second;
   for (int j = 0; j < 2; j++) cudaFree(c->d_set[j]);
+  if (c->d_motion_draws) cudaFree(c->d_motion_draws);
   cudaFree(c->d_cum); cudaFree(c->d_draws); cudaFree(c->d_src); cudaFree(c->d_label);
   cudaFree(c->d_keys); cudaFree(c->d_slot); cudaFree(c->d_flag); cudaFree(c->d_scan);
   cudaFree(c->d_scan_tiles); cudaFree(c->d_hash); cudaFree(c->d_scalars); cudaFree(c->d_ints);
@@ -113,9 +116,20 @@ void pf_ctx_release(pf_t *pf)
   r.erase(it);
 }
 
+void pf_replicate(PfCtx *c, int which)
+{
+  if (!c->shard.on() || c->replicated[which]) return;
+  const int n = c->host->sets[which].sample_count;
+  if (n > 0)
+    c->shard.allgather(c->d_set[which],
+                       (unsigned long long)c->shard.chunk(n) * sizeof(Particle), c->shard.user);
+  c->replicated[which] = true;
+}
+
 void pf_pull(PfCtx *c, int which)
 {
   if (c->host_fresh[which]) return;
+  pf_replicate(c, which);   // a collective when sharded: every rank pulls together
   pf_sample_set_t *set = c->host->sets + which;
   if (set->sample_count > 0)
     AMCL_CUDA(cudaMemcpyAsync(set->samples, c->d_set[which],
@@ -136,6 +150,7 @@ void pf_push(PfCtx *c, int which)
                               cudaMemcpyHostToDevice, globals().stream));
   AMCL_CUDA(cudaStreamSynchronize(globals().stream));
   c->host_fresh[which] = true;
+  c->replicated[which] = true;
 }
 
 void pf_after_update(PfCtx *c, int which)

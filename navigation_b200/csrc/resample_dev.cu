@@ -272,7 +272,9 @@ struct PickArgs
   Particle *dst;
   int *src_index;
   unsigned long long *keys;
-  int count;
+  int first;                // first candidate index handled by this launch
+  int count;                // number of candidates handled
+  int write_keys;           // 0: poses only (re-pick after the cut)
   double bin_x, bin_y, bin_t;
 };
 
@@ -281,8 +283,9 @@ struct PickArgs
 // rescaled once n is known.
 __global__ void pick_and_copy(const PickArgs a)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= a.count) return;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= a.count) return;
+  const int m = a.first + t;
   Particle s;
   int from = -1;
   if (a.inject_slot && a.inject_slot[m] >= 0)
@@ -304,7 +307,7 @@ __global__ void pick_and_copy(const PickArgs a)
   s.w = 1.0;
   store_particle(a.dst + m, s);
   a.src_index[m] = from;
-  a.keys[m] = pose_key(s, a.bin_x, a.bin_y, a.bin_t);
+  if (a.write_keys) a.keys[m] = pose_key(s, a.bin_x, a.bin_y, a.bin_t);
 }
 
 __global__ void keys_of_set(const Particle *__restrict__ set, int n, unsigned long long *keys,
@@ -551,8 +554,12 @@ __global__ void cluster_accumulate(const Particle *__restrict__ set, int n,
                                    const HashSlot *__restrict__ table,
                                    const unsigned int *__restrict__ slot_of,
                                    const unsigned int *__restrict__ cid_of_root, double *acc,
-                                   int *label_out)
+                                   int *label_out, int first)
 {
+  // samples [first, first + n) of the set (a sharded rank sums its own slice)
+  set += first;
+  slot_of += first;
+  if (label_out) label_out += first;
   const int lane = threadIdx.x & 31;
   const int warps_per_block = blockDim.x >> 5;
   const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
@@ -799,10 +806,16 @@ static void build_histogram(PfCtx *c, int count)
 // (d_keys/d_slot/d_flag/d_hash) must describe at least those samples.
 static void cluster_and_stats(PfCtx *c, int which, int n)
 {
+  // Labelling runs on the whole (replicated) histogram on every rank and is
+  // deterministic, so all ranks agree on the labels; the per-sample sums are
+  // taken over the owned slice only and all-reduced.
+  const bool sliced = c->shard.on() && !c->replicated[which];
+  const int acc_lo = sliced ? c->shard.lo(n) : 0;
+  const int acc_cnt = sliced ? c->shard.count(n) : n;
   cudaStream_t st = globals().stream;
   pf_t *pf = c->host;
   pf_sample_set_t *set = pf->sets + which;
-  unsigned int *cmin = c->d_scan + c->max_samples;  // second half: per-slot scratch (hash_cap)
+  unsigned int *cmin = c->d_scan + c->alloc_samples;  // second half: per-slot scratch (hash_cap)
   const int nb = blocks_for(n, 256);
 
   cc_init<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin);
@@ -816,7 +829,7 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
   AMCL_LAUNCH_CHECK();
   // cluster-opening flags reuse d_keys' storage as u32 scratch (keys are spent)
   unsigned int *cflag = reinterpret_cast<unsigned int *>(c->d_keys);
-  unsigned int *cscan = cflag + c->max_samples;
+  unsigned int *cscan = cflag + c->alloc_samples;
   cc_mark_cluster_first<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin, cflag);
   AMCL_LAUNCH_CHECK();
   scan_u32(c, cflag, cscan, n, I_CLUSTERS);
@@ -834,11 +847,14 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
   AMCL_CUDA(cudaMemsetAsync(c->d_cluster_acc, 0, sizeof(double) * 10 * (size_t)(ncl > 0 ? ncl : 1), st));
   {
     int grid = globals().sm_count * 8;
-    if (grid > nb) grid = nb;
-    cluster_accumulate<<<grid, 256, 0, st>>>(c->d_set[which], n, c->d_hash, c->d_slot, cmin,
-                                             c->d_cluster_acc, c->d_label);
+    const int need = blocks_for(acc_cnt, 256);
+    if (grid > need) grid = need;
+    cluster_accumulate<<<grid, 256, 0, st>>>(c->d_set[which], acc_cnt, c->d_hash, c->d_slot, cmin,
+                                             c->d_cluster_acc, c->d_label, acc_lo);
   }
   AMCL_LAUNCH_CHECK();
+  if (sliced && ncl > 0)
+    c->shard.allreduce(c->d_cluster_acc, 10 * ncl, SHARD_F64, SHARD_SUM, c->shard.user);
   std::vector<double> acc((size_t)10 * (ncl > 0 ? ncl : 1));
   AMCL_CUDA(cudaMemcpyAsync(acc.data(), c->d_cluster_acc, sizeof(double) * 10 * (size_t)ncl,
                             cudaMemcpyDeviceToHost, st));
@@ -893,6 +909,7 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
 
 void run_cluster_stats(PfCtx *c, int which, bool histogram_ready)
 {
+  if (!histogram_ready) pf_replicate(c, which);   // keys are needed for every sample
   cudaStream_t st = globals().stream;
   pf_sample_set_t *set = c->host->sets + which;
   const int n = set->sample_count;
@@ -910,22 +927,41 @@ void run_cluster_stats(PfCtx *c, int which, bool histogram_ready)
   cluster_and_stats(c, which, n);
 }
 
+__global__ void divide_pair(double *v, int n)
+{
+  v[0] = v[0] / n;
+  v[1] = v[1] / n;
+}
+
 int run_update_converged(PfCtx *c, int which)
 {
   cudaStream_t st = globals().stream;
   pf_t *pf = c->host;
   pf_sample_set_t *set = pf->sets + which;
   const int n = set->sample_count;
-  const int grid = reduce_grid(n);
+  const bool sliced = c->shard.on() && !c->replicated[which];
+  const int lo = sliced ? c->shard.lo(n) : 0;
+  const int cnt = sliced ? c->shard.count(n) : n;
+  const Particle *base = c->d_set[which] + lo;
+  const int grid = reduce_grid(cnt);
   ensure_partials(c, 2 * grid);
-  sum_xy<<<grid, 256, 0, st>>>(c->d_set[which], n, c->d_partials, c->d_partials + grid);
+  sum_xy<<<grid, 256, 0, st>>>(base, cnt, c->d_partials, c->d_partials + grid);
   AMCL_LAUNCH_CHECK();
-  finish_xy<<<1, 256, 0, st>>>(c->d_partials, c->d_partials + grid, grid, n, c->d_scalars + 4);
+  if (!sliced)
+    finish_xy<<<1, 256, 0, st>>>(c->d_partials, c->d_partials + grid, grid, n, c->d_scalars + 4);
+  else
+  {
+    finish_xy<<<1, 256, 0, st>>>(c->d_partials, c->d_partials + grid, grid, 1, c->d_scalars + 4);
+    AMCL_LAUNCH_CHECK();
+    c->shard.allreduce(c->d_scalars + 4, 2, SHARD_F64, SHARD_SUM, c->shard.user);
+    divide_pair<<<1, 1, 0, st>>>(c->d_scalars + 4, n);
+  }
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaMemsetAsync(c->d_ints + I_OUTSIDE, 0, sizeof(int), st));
-  any_outside<<<grid, 256, 0, st>>>(c->d_set[which], n, c->d_scalars + 4, pf->dist_threshold,
+  any_outside<<<grid, 256, 0, st>>>(base, cnt, c->d_scalars + 4, pf->dist_threshold,
                                     c->d_ints + I_OUTSIDE);
   AMCL_LAUNCH_CHECK();
+  if (sliced) c->shard.allreduce(c->d_ints + I_OUTSIDE, 1, SHARD_I32, SHARD_MAX, c->shard.user);
   sync_ints(c, I_OUTSIDE, 1);
   const int conv = c->h_ints[I_OUTSIDE] ? 0 : 1;
   set->converged = conv;
@@ -935,6 +971,7 @@ int run_update_converged(PfCtx *c, int which)
 
 void run_cep_stats(PfCtx *c, int which, double out[4])
 {
+  pf_replicate(c, which);
   cudaStream_t st = globals().stream;
   pf_sample_set_t *set = c->host->sets + which;
   const int n = set->sample_count;
@@ -951,6 +988,8 @@ void run_cep_stats(PfCtx *c, int which, double out[4])
 // copy_set (pf.c:321-360): b = a with weights renormalised by their sum.
 void run_copy_set(PfCtx *c, int from, int to)
 {
+  pf_replicate(c, from);
+  c->replicated[to] = true;
   cudaStream_t st = globals().stream;
   pf_t *pf = c->host;
   const int n = pf->sets[from].sample_count;
@@ -977,6 +1016,11 @@ void run_resample(PfCtx *c)
   pf_sample_set_t *set_a = pf->sets + ia, *set_b = pf->sets + ib;
   const int n_a = set_a->sample_count;
   const int maxs = pf->max_samples;
+  const Shard &sh = c->shard;
+
+  // Draws range over the GLOBAL table: a sharded run
+  // first makes the whole source set present on every rank.
+  pf_replicate(c, ia);
 
   // pf.c:378-394
   if (pf->selective_resampling != 0 && set_a->n_effective > 0.5 * (set_a->sample_count))
@@ -1074,10 +1118,18 @@ void run_resample(PfCtx *c)
   pa.dst = c->d_set[ib];
   pa.src_index = c->d_src;
   pa.keys = c->d_keys;
-  pa.count = maxs;
+  pa.write_keys = 1;
+  // a sharded rank picks only its slice of the candidate samples ...
+  pa.first = sh.lo(maxs);
+  pa.count = sh.count(maxs);
   bin_sizes(set_b, &pa.bin_x, &pa.bin_y, &pa.bin_t);
-  pick_and_copy<<<blocks_for(maxs, 256), 256, 0, st>>>(pa);
+  pick_and_copy<<<blocks_for(pa.count, 256), 256, 0, st>>>(pa);
   AMCL_LAUNCH_CHECK();
+  // ... and the bin keys of all candidates are exchanged: the KLD count below
+  // is a property of the global sample ORDER, so every rank evaluates it on the
+  // full key list and reaches the same n and k without further traffic.
+  if (sh.on())
+    sh.allgather(c->d_keys, (unsigned long long)sh.chunk(maxs) * sizeof(unsigned long long), sh.user);
 
   // ---- histogram, k_m, KLD cut ---------------------------------------------
   build_histogram(c, maxs);
@@ -1098,12 +1150,6 @@ void run_resample(PfCtx *c)
   set_b->sample_count = n;
   set_b->kdtree->leaf_count = (int)k_at_cut;
 
-  if (d_injected)
-  {
-    cudaFree(d_injected);
-    cudaFree(d_inject_slot);
-  }
-
   if (host_stream)
   {
     // leave libc's stream where the reference would have left it: replay the
@@ -1120,10 +1166,32 @@ void run_resample(PfCtx *c)
   // pf.c:487-489
   if (w_diff > 0.0) pf->w_slow = pf->w_fast = 0.0;
 
+  const int own_lo = sh.lo(n), own_cnt = sh.count(n);
+  if (sh.on() && n != maxs && own_cnt > 0)
+  {
+    // The cut changed the slicing (slices of n, not of max_samples).  Picking
+    // is a pure function of (table, draw m), so each rank simply re-picks the
+    // poses of its NEW slice instead of fetching them from their old owners.
+    pa.first = own_lo;
+    pa.count = own_cnt;
+    pa.write_keys = 0;
+    pick_and_copy<<<blocks_for(own_cnt, 256), 256, 0, st>>>(pa);
+    AMCL_LAUNCH_CHECK();
+  }
   // pf.c:493-498: every weight is 1/n
-  set_uniform_weight<<<blocks_for(n, 256), 256, 0, st>>>(c->d_set[ib], n, 1.0 / (double)n);
-  AMCL_LAUNCH_CHECK();
+  if (own_cnt > 0)
+  {
+    set_uniform_weight<<<blocks_for(own_cnt, 256), 256, 0, st>>>(c->d_set[ib] + own_lo, own_cnt,
+                                                                 1.0 / (double)n);
+    AMCL_LAUNCH_CHECK();
+  }
   c->host_fresh[ib] = false;
+  c->replicated[ib] = !sh.on();
+  if (d_injected)
+  {
+    cudaFree(d_injected);     // synchronises; the picks above are done with it
+    cudaFree(d_inject_slot);
+  }
 
   // pf.c:501-506
   cluster_and_stats(c, ib, n);

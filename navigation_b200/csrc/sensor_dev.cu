@@ -424,7 +424,9 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
 {
   (void)n_beam_slots;
   cudaStream_t st = globals().stream;
-  const int n = c->host->sets[which].sample_count;
+  const int n_all = c->host->sets[which].sample_count;
+  const int lo = c->shard.lo(n_all);
+  const int n = c->shard.count(n_all);     // this rank's slice (everything when not sharded)
   // beam table: only beams that are integrated (mask applied on the host)
   std::vector<double> tab;
   std::vector<int> used;
@@ -475,7 +477,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   }
 
   LfArgs a;
-  a.set = c->d_set[which];
+  a.set = c->d_set[which] + lo;
   a.n = n;
   a.beams = reinterpret_cast<const double2 *>(c->d_scan_tab);
   a.nb = nb;
@@ -539,6 +541,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
 
   if (count_mode)
   {
+    if (c->shard.on() && nb > 0) c->shard.allreduce(d_counts, nb, SHARD_I32, SHARD_SUM, c->shard.user);
     std::vector<int> counts((size_t)nb + 1);
     AMCL_CUDA(cudaMemcpyAsync(counts.data(), d_counts, sizeof(int) * (size_t)nb,
                               cudaMemcpyDeviceToHost, st));
@@ -548,6 +551,11 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   }
   finish_partials<<<1, 256, 0, st>>>(c->d_partials, grid, c->d_scalars, 0);
   AMCL_LAUNCH_CHECK();
+  if (c->shard.on())
+  {
+    c->shard.allreduce(c->d_scalars, 1, SHARD_F64, SHARD_SUM, c->shard.user);
+    c->replicated[which] = false;
+  }
   const double total = read_scalar(c, 0);  // also orders the staging vectors' lifetime
   AMCL_CUDA(cudaEventElapsedTime(&c->ms_sensor_kernel, c->ev_a, c->ev_b));
   c->sensor_evals = (long long)n * nb;
@@ -559,7 +567,9 @@ double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3]
                       const LaserScanHost &scan, double range_max, const double zp[6])
 {
   cudaStream_t st = globals().stream;
-  const int n = c->host->sets[which].sample_count;
+  const int n_all = c->host->sets[which].sample_count;
+  const int lo = c->shard.lo(n_all);
+  const int n = c->shard.count(n_all);
   const int nb = (int)scan.range.size();
   // zp: z_hit, z_short, z_max, z_rand, sigma_hit, lambda_short
   std::vector<double> tab((size_t)(nb > 0 ? nb : 1) * 5 + 2, 0.0);
@@ -584,7 +594,7 @@ double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3]
   AMCL_CUDA(cudaMemcpyAsync(c->d_scan_tab, tab.data(), tab.size() * sizeof(double),
                             cudaMemcpyHostToDevice, st));
   BeamArgs a;
-  a.set = c->d_set[which];
+  a.set = c->d_set[which] + lo;
   a.n = n;
   a.tab = c->d_scan_tab;
   a.nb = nb;
@@ -611,6 +621,11 @@ double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3]
   AMCL_LAUNCH_CHECK();
   finish_partials<<<1, 256, 0, st>>>(c->d_partials, grid, c->d_scalars, 0);
   AMCL_LAUNCH_CHECK();
+  if (c->shard.on())
+  {
+    c->shard.allreduce(c->d_scalars, 1, SHARD_F64, SHARD_SUM, c->shard.user);
+    c->replicated[which] = false;
+  }
   const double total = read_scalar(c, 0);
   c->host_fresh[which] = false;
   return total;
@@ -621,18 +636,23 @@ void run_sensor_normalise(PfCtx *c, int which, double total)
   cudaStream_t st = globals().stream;
   pf_t *pf = c->host;
   pf_sample_set_t *set = pf->sets + which;
-  const int n = set->sample_count;
+  const int n = set->sample_count;                 // the global count
+  // a foreign host model rewrote the whole (replicated) set: normalise all of it
+  const bool slice = c->shard.on() && !c->replicated[which];
+  const int lo = slice ? c->shard.lo(n) : 0;
+  const int cnt = slice ? c->shard.count(n) : n;
   int grid = globals().sm_count * 4;
-  int need_blocks = (n + 255) / 256;
+  int need_blocks = (cnt + 255) / 256;
   if (grid > need_blocks) grid = need_blocks > 0 ? need_blocks : 1;
   ensure_partials(c, grid);
-  normalise_weights<<<grid, 256, 0, st>>>(c->d_set[which], n, total, 1.0 / n, c->d_partials);
+  normalise_weights<<<grid, 256, 0, st>>>(c->d_set[which] + lo, cnt, total, 1.0 / n, c->d_partials);
   AMCL_LAUNCH_CHECK();
   double neff = 0.0;
   if (total > 0.0)
   {
     finish_partials<<<1, 256, 0, st>>>(c->d_partials, grid, c->d_scalars, 1);
     AMCL_LAUNCH_CHECK();
+    if (slice) c->shard.allreduce(c->d_scalars + 1, 1, SHARD_F64, SHARD_SUM, c->shard.user);
     neff = read_scalar(c, 1);
     // pf.c:293-302.  w_avg accumulates the very numbers the model summed into
     // `total`, in the same order, so it equals total / n.

@@ -32,6 +32,9 @@ EXTENSION_SYMBOLS = {
     "amclb200_pf_last_timings": (None, [abi.pf_p, C.POINTER(C.c_float)]),
     "amclb200_map_calc_ranges": (None, [abi.map_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p]),
     "amclb200_pf_load_device": (None, [abi.pf_p, C.c_void_p, C.c_int]),
+    "amclb200_pf_set_shard": (None, [abi.pf_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "amclb200_pf_load_device_shard": (None, [abi.pf_p, C.c_void_p, C.c_int]),
+    "amclb200_pf_shard_range": (None, [abi.pf_p, C.c_int, C.POINTER(C.c_int)]),
     "amclb200_launch_count": (C.c_uint64, []),
     "amclb200_pf_best_cluster": (C.c_int, [abi.pf_p, abi.c_double_p, C.POINTER(abi.pf_vector_t), C.POINTER(abi.pf_matrix_t)]),
     "amclb200_cumsum_fallbacks": (C.c_uint64, []),
