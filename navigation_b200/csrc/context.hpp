@@ -80,12 +80,6 @@ void map_codes_from_host_cells(MapCtx *m);       // encodes cells[].occ_dist
 
 // ---- particle filter -------------------------------------------------------------
 
-struct HashSlot
-{
-  unsigned long long key;   // packed bin key, kEmptyKey when free
-  unsigned int first;       // smallest sample index that landed here
-  unsigned int aux;         // union-find parent, later the cluster id
-};
 constexpr unsigned long long kEmptyKey = ~0ull;
 
 // ---- sharding over GPUs -------------------------------------------------------------
@@ -140,8 +134,13 @@ struct PfCtx
   unsigned int *d_scan_tiles = nullptr;  // per-tile sums of the u32 scan
   int scan_tiles_cap = 0;
   int *d_label = nullptr;         // cluster label per sample (canonical numbering)
-  HashSlot *d_hash = nullptr;
+  // bin table (see resample_dev.cu): parallel arrays of hash_cap slots
+  unsigned long long *d_tab_key = nullptr;
+  unsigned int *d_tab_first = nullptr;
+  unsigned int *d_tab_aux = nullptr;
   unsigned int hash_cap = 0;      // power of two
+  int tab_dense = 0;              // last histogram: dense grid (1) or hash (0)
+  int tab_lo[3] = {0, 0, 0}, tab_ext[3] = {0, 0, 0};
   double *d_cluster_acc = nullptr;  // [cluster][10]
   int cluster_acc_cap = 0;
   double *d_partials = nullptr;   // per-block partial sums (several lanes)

@@ -82,7 +82,9 @@ PfCtx *pf_ctx_create(pf_t *pf)
   AMCL_CUDA(cudaMalloc(&c->d_scan, sizeof(unsigned int) * (maxs + c->hash_cap)));
   c->scan_tiles_cap = (int)(maxs / 4096 + 4);
   AMCL_CUDA(cudaMalloc(&c->d_scan_tiles, sizeof(unsigned int) * (size_t)c->scan_tiles_cap));
-  AMCL_CUDA(cudaMalloc(&c->d_hash, sizeof(HashSlot) * (size_t)c->hash_cap));
+  AMCL_CUDA(cudaMalloc(&c->d_tab_key, sizeof(unsigned long long) * (size_t)c->hash_cap));
+  AMCL_CUDA(cudaMalloc(&c->d_tab_first, sizeof(unsigned int) * (size_t)c->hash_cap));
+  AMCL_CUDA(cudaMalloc(&c->d_tab_aux, sizeof(unsigned int) * (size_t)c->hash_cap));
   AMCL_CUDA(cudaMalloc(&c->d_scalars, sizeof(double) * 64));
   AMCL_CUDA(cudaMalloc(&c->d_ints, sizeof(int) * 64));
   AMCL_CUDA(cudaMallocHost(&c->h_scalars, sizeof(double) * 64));
@@ -101,7 +103,7 @@ void pf_ctx_release(pf_t *pf)
   if (c->d_motion_draws) cudaFree(c->d_motion_draws);
   cudaFree(c->d_cum); cudaFree(c->d_draws); cudaFree(c->d_src); cudaFree(c->d_label);
   cudaFree(c->d_keys); cudaFree(c->d_slot); cudaFree(c->d_flag); cudaFree(c->d_scan);
-  cudaFree(c->d_scan_tiles); cudaFree(c->d_hash); cudaFree(c->d_scalars); cudaFree(c->d_ints);
+  cudaFree(c->d_scan_tiles); cudaFree(c->d_tab_key); cudaFree(c->d_tab_first); cudaFree(c->d_tab_aux); cudaFree(c->d_scalars); cudaFree(c->d_ints);
   if (c->d_cluster_acc) cudaFree(c->d_cluster_acc);
   if (c->d_partials) cudaFree(c->d_partials);
   if (c->d_scan_tab) cudaFree(c->d_scan_tab);

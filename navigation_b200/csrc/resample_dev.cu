@@ -319,33 +319,101 @@ __global__ void keys_of_set(const Particle *__restrict__ set, int n, unsigned lo
 }
 
 // ------------------------------------------------------------ pose histogram --
+//
+// The histogram of occupied bins (the reference's kd-tree leaves) lives in three
+// parallel arrays indexed by SLOT: first[] = smallest sample index that fell
+// into the bin, aux[] = union-find parent / root, key[] = packed bin key.
+//  * DENSE mode: when the bounding box of the keys is small enough (it always
+//    is for poses on a map: 400 x 400 x ~40 bins for a 200 m map), a slot IS a
+//    cell of a 3-D grid over that box.  Insertion is one atomicMin, neighbour
+//    lookup is index arithmetic, and the 4-byte arrays stay L2-resident.
+//  * HASH mode (any other case): open addressing on the 64-bit key.
+struct BinTable
+{
+  unsigned long long *key;   // hash mode only
+  unsigned int *first;
+  unsigned int *aux;
+  unsigned int mask;         // hash mode: capacity - 1
+  int dense;
+  int x0, y0, t0;            // dense: smallest key per axis
+  int ex, ey, et;            // dense: extent per axis
+};
 
-__global__ void hash_insert(const unsigned long long *__restrict__ keys, int n, HashSlot *table,
-                            unsigned int mask, unsigned int *slot_of)
+__host__ __device__ inline void unpack_key(unsigned long long k, int *kx, int *ky, int *kt)
+{
+  *kx = (int)(k >> 43) - kBiasXY;
+  *ky = (int)((k >> 22) & 0x1FFFFFull) - kBiasXY;
+  *kt = (int)(k & 0x3FFFFFull) - kBiasTh;
+}
+
+// min / max of each key component: out = {minx, miny, mint, maxx, maxy, maxt}
+__global__ void key_bounds(const unsigned long long *__restrict__ keys, int n, int *out)
+{
+  int lo[3] = {0x7FFFFFFF, 0x7FFFFFFF, 0x7FFFFFFF}, hi[3] = {-0x7FFFFFFF, -0x7FFFFFFF, -0x7FFFFFFF};
+  for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < n; m += gridDim.x * blockDim.x)
+  {
+    int k[3];
+    unpack_key(keys[m], &k[0], &k[1], &k[2]);
+#pragma unroll
+    for (int q = 0; q < 3; q++)
+    {
+      lo[q] = min(lo[q], k[q]);
+      hi[q] = max(hi[q], k[q]);
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 3; q++)
+  {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+      lo[q] = min(lo[q], __shfl_xor_sync(kFullMask, lo[q], o));
+      hi[q] = max(hi[q], __shfl_xor_sync(kFullMask, hi[q], o));
+    }
+    if ((threadIdx.x & 31) == 0)
+    {
+      atomicMin(&out[q], lo[q]);
+      atomicMax(&out[3 + q], hi[q]);
+    }
+  }
+}
+
+__global__ void bin_insert(const unsigned long long *__restrict__ keys, int n, const BinTable T,
+                           unsigned int *slot_of)
 {
   const int m = blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= n) return;
   const unsigned long long key = keys[m];
-  unsigned int h = hash_key(key) & mask;
+  if (T.dense)
+  {
+    int kx, ky, kt;
+    unpack_key(key, &kx, &ky, &kt);
+    const unsigned int cell =
+        (unsigned int)(((kt - T.t0) * T.ey + (ky - T.y0)) * T.ex + (kx - T.x0));
+    atomicMin(&T.first[cell], (unsigned int)m);
+    slot_of[m] = cell;
+    return;
+  }
+  unsigned int h = hash_key(key) & T.mask;
   for (;;)
   {
-    const unsigned long long prev = atomicCAS(&table[h].key, kEmptyKey, key);
+    const unsigned long long prev = atomicCAS(&T.key[h], kEmptyKey, key);
     if (prev == kEmptyKey || prev == key)
     {
-      atomicMin(&table[h].first, (unsigned int)m);
+      atomicMin(&T.first[h], (unsigned int)m);
       slot_of[m] = h;
       return;
     }
-    h = (h + 1) & mask;
+    h = (h + 1) & T.mask;
   }
 }
 
-__global__ void mark_first(const HashSlot *__restrict__ table, const unsigned int *__restrict__ slot_of,
+__global__ void mark_first(const unsigned int *__restrict__ first, const unsigned int *__restrict__ slot_of,
                            int n, unsigned int *flag)
 {
   const int m = blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= n) return;
-  flag[m] = table[slot_of[m]].first == (unsigned int)m ? 1u : 0u;
+  flag[m] = first[slot_of[m]] == (unsigned int)m ? 1u : 0u;
 }
 
 // pf.c:515-555 with IEEE ops in source order and no contraction.  The final
@@ -396,111 +464,122 @@ __global__ void set_uniform_weight(Particle *set, int n, double w)
 
 // Parent pointers are read with L2 (.cg) loads: L1 is not coherent across SMs
 // and a stale "I am a root" would make the CAS in uf_union spin.
-__device__ __forceinline__ unsigned int uf_find(HashSlot *t, unsigned int x)
+__device__ __forceinline__ unsigned int uf_find(unsigned int *aux, unsigned int x)
 {
-  unsigned int p = __ldcg(&t[x].aux);
+  unsigned int p = __ldcg(&aux[x]);
   while (p != x)
   {
-    const unsigned int gp = __ldcg(&t[p].aux);
-    if (gp != p) t[x].aux = gp;  // path halving (benign race: gp is an ancestor)
+    const unsigned int gp = __ldcg(&aux[p]);
+    if (gp != p) aux[x] = gp;  // path halving (benign race: gp is an ancestor)
     x = p;
     p = gp;
   }
   return x;
 }
 
-__device__ __forceinline__ void uf_union(HashSlot *t, unsigned int a, unsigned int b)
+__device__ __forceinline__ void uf_union(unsigned int *aux, unsigned int a, unsigned int b)
 {
   for (;;)
   {
-    a = uf_find(t, a);
-    b = uf_find(t, b);
+    a = uf_find(aux, a);
+    b = uf_find(aux, b);
     if (a == b) return;
     if (a > b) { unsigned int s = a; a = b; b = s; }
     // hang the larger root under the smaller one
-    if (atomicCAS(&t[b].aux, b, a) == b) return;
+    if (atomicCAS(&aux[b], b, a) == b) return;
   }
 }
 
-// every occupied bin (first sample < n_valid) starts as its own component
-__global__ void cc_init(HashSlot *table, const unsigned int *__restrict__ slot_of,
-                        const unsigned int *__restrict__ flag, int n_valid, unsigned int *cmin)
+// The labelling kernels below run ONE THREAD PER TABLE SLOT (grid cell or hash
+// slot), not per sample: neighbouring threads then work on neighbouring bins,
+// the arrays are read in order, and the unions arrive in a scan-line-like
+// pattern that keeps the trees shallow.  A slot is occupied when a sample below
+// n_valid fell into it (empty slots hold 0xFFFFFFFF).
+
+// every occupied bin starts as its own component
+__global__ void cc_init(const BinTable T, unsigned int nslots, int n_valid, unsigned int *cmin)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= n_valid || !flag[m]) return;
-  const unsigned int s = slot_of[m];
-  table[s].aux = s;
+  const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  T.aux[s] = s;
   cmin[s] = 0xFFFFFFFFu;
 }
 
 // pf_kdtree.c:407-438: bins are neighbours when every key component differs
-// by at most one (26-neighbourhood, heading NOT wrapped).
-__global__ void cc_link(HashSlot *table, unsigned int mask, const unsigned int *__restrict__ slot_of,
-                        const unsigned int *__restrict__ flag, int n_valid)
+// by at most one (26-neighbourhood, heading NOT wrapped).  Only the 13
+// "forward" neighbours are visited: the relation is symmetric.
+__global__ void cc_link(const BinTable T, unsigned int nslots, int n_valid)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= n_valid || !flag[m]) return;
-  const unsigned int s = slot_of[m];
-  const unsigned long long key = table[s].key;
-  // only the 13 "forward" neighbours: the relation is symmetric
+  const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (T.dense)
+  {
+    const int ix = (int)(s % (unsigned)T.ex);
+    const int iy = (int)((s / (unsigned)T.ex) % (unsigned)T.ey);
+    const int it = (int)(s / ((unsigned)T.ex * (unsigned)T.ey));
+    for (int q = 14; q < 27; q++)
+    {
+      const int dt = q / 9 - 1, dy = (q % 9) / 3 - 1, dx = (q % 9) % 3 - 1;   // x fastest
+      const int nx = ix + dx, ny = iy + dy, nt = it + dt;
+      if ((unsigned)nx >= (unsigned)T.ex || (unsigned)ny >= (unsigned)T.ey ||
+          (unsigned)nt >= (unsigned)T.et)
+        continue;
+      const unsigned int nb = (unsigned int)((nt * T.ey + ny) * T.ex + nx);
+      if (T.first[nb] < (unsigned int)n_valid) uf_union(T.aux, s, nb);
+    }
+    return;
+  }
+  const unsigned long long key = T.key[s];
   for (int q = 14; q < 27; q++)
   {
     const long long dx = q / 9 - 1, dy = (q % 9) / 3 - 1, dt = (q % 9) % 3 - 1;
     const unsigned long long nk = key + (unsigned long long)(dx * (1ll << 43) + dy * (1ll << 22) + dt);
-    unsigned int h = hash_key(nk) & mask;
+    unsigned int h = hash_key(nk) & T.mask;
     for (;;)
     {
-      const unsigned long long kk = table[h].key;
+      const unsigned long long kk = T.key[h];
       if (kk == kEmptyKey) break;
       if (kk == nk)
       {
-        if (table[h].first < (unsigned int)n_valid) uf_union(table, s, h);
+        if (T.first[h] < (unsigned int)n_valid) uf_union(T.aux, s, h);
         break;
       }
-      h = (h + 1) & mask;
+      h = (h + 1) & T.mask;
     }
   }
 }
 
-// Read-only find: no path halving, so it can run while nothing else writes.
-__device__ __forceinline__ unsigned int uf_find_ro(const HashSlot *t, unsigned int x)
+// One round of pointer jumping: every bin adopts its grandparent.  Repeated
+// until nothing moves (depth halves per round), every bin points at its root.
+__global__ void cc_jump(const BinTable T, unsigned int nslots, int n_valid, int *moved)
 {
-  unsigned int p = __ldcg(&t[x].aux);
-  while (p != x)
+  const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  const unsigned int p = __ldcg(&T.aux[s]);
+  const unsigned int gp = __ldcg(&T.aux[p]);
+  if (gp != p)
   {
-    x = p;
-    p = __ldcg(&t[x].aux);
+    T.aux[s] = gp;
+    *moved = 1;
   }
-  return x;
 }
 
-// Root of every occupied bin and the smallest first-sample index per
-// component.  The root goes to a side array first: writing it into aux here
-// would race with other threads still walking the parent chains.
-__global__ void cc_roots(const HashSlot *__restrict__ table, const unsigned int *__restrict__ slot_of,
-                         const unsigned int *__restrict__ flag, int n_valid, unsigned int *cmin,
-                         unsigned int *root_of_first)
+// smallest first-sample index of every component, kept at its root
+__global__ void cc_component_min(const BinTable T, unsigned int nslots, int n_valid,
+                                 unsigned int *cmin)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= n_valid || !flag[m]) return;
-  const unsigned int r = uf_find_ro(table, slot_of[m]);
-  root_of_first[m] = r;
-  atomicMin(&cmin[r], (unsigned int)m);
-}
-
-// every occupied bin now points straight at its root
-__global__ void cc_flatten(HashSlot *table, const unsigned int *__restrict__ slot_of,
-                           const unsigned int *__restrict__ flag, int n_valid,
-                           const unsigned int *__restrict__ root_of_first)
-{
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= n_valid || !flag[m]) return;
-  table[slot_of[m]].aux = root_of_first[m];
+  const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots) return;
+  const unsigned int f = T.first[s];
+  if (f >= (unsigned int)n_valid) return;
+  // A giant component would otherwise serialise millions of atomics on one
+  // address: look first, and only compete when this bin can lower the value.
+  unsigned int *slot = &cmin[T.aux[s]];
+  if (f < __ldcg(slot)) atomicMin(slot, f);
 }
 
 // a sample opens a new cluster when it is the earliest sample of its component
-__global__ void cc_mark_cluster_first(const HashSlot *__restrict__ table,
-                                      const unsigned int *__restrict__ slot_of,
+__global__ void cc_mark_cluster_first(const BinTable T, const unsigned int *__restrict__ slot_of,
                                       const unsigned int *__restrict__ flag, int n_valid,
                                       const unsigned int *__restrict__ cmin, unsigned int *cflag)
 {
@@ -509,7 +588,7 @@ __global__ void cc_mark_cluster_first(const HashSlot *__restrict__ table,
   unsigned int f = 0;
   if (flag[m])
   {
-    const unsigned int r = table[slot_of[m]].aux;   // root (set by cc_roots)
+    const unsigned int r = T.aux[slot_of[m]];   // root (set by cc_flatten)
     f = cmin[r] == (unsigned int)m ? 1u : 0u;
   }
   cflag[m] = f;
@@ -517,13 +596,13 @@ __global__ void cc_mark_cluster_first(const HashSlot *__restrict__ table,
 
 // cluster id of a component = (number of cluster-opening samples before its
 // first sample); stored over cmin[root]
-__global__ void cc_assign_ids(const HashSlot *__restrict__ table, const unsigned int *__restrict__ slot_of,
+__global__ void cc_assign_ids(const BinTable T, const unsigned int *__restrict__ slot_of,
                               const unsigned int *__restrict__ cflag,
                               const unsigned int *__restrict__ cscan, int n_valid, unsigned int *cid)
 {
   const int m = blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= n_valid || !cflag[m]) return;
-  const unsigned int r = table[slot_of[m]].aux;
+  const unsigned int r = T.aux[slot_of[m]];
   cid[r] = cscan[m] - 1u;
 }
 
@@ -551,7 +630,7 @@ __device__ __forceinline__ void flush_hot(double *acc, unsigned int hot, double 
 }
 
 __global__ void cluster_accumulate(const Particle *__restrict__ set, int n,
-                                   const HashSlot *__restrict__ table,
+                                   const unsigned int *__restrict__ root_of_slot,
                                    const unsigned int *__restrict__ slot_of,
                                    const unsigned int *__restrict__ cid_of_root, double *acc,
                                    int *label_out, int first)
@@ -580,7 +659,7 @@ __global__ void cluster_accumulate(const Particle *__restrict__ set, int n,
     if (live)
     {
       const Particle s = load_particle(set + i);
-      const unsigned int root = table[slot_of[i]].aux;
+      const unsigned int root = root_of_slot[slot_of[i]];
       label = cid_of_root[root];
       double sn, cs;
       sincos(s.th, &sn, &cs);
@@ -781,7 +860,7 @@ static void sync_scalars(PfCtx *c, int first, int count)
 }
 
 // d_ints slots
-enum { I_DISTINCT = 0, I_CUT = 1, I_CLUSTERS = 2, I_OUTSIDE = 3 };
+enum { I_DISTINCT = 0, I_CUT = 1, I_CLUSTERS = 2, I_OUTSIDE = 3, I_MOVED = 4 };
 
 static void bin_sizes(const pf_sample_set_t *set, double *bx, double *by, double *bt)
 {
@@ -791,14 +870,55 @@ static void bin_sizes(const pf_sample_set_t *set, double *bx, double *by, double
 }
 
 // Histogram over samples [0, count) of `which` from precomputed keys.
+// d_ints slots 16..21 hold the key bounds
+enum { I_BOUNDS = 16 };
+
+static BinTable table_of(const PfCtx *c)
+{
+  BinTable T;
+  T.key = c->d_tab_key;
+  T.first = c->d_tab_first;
+  T.aux = c->d_tab_aux;
+  T.mask = c->hash_cap - 1;
+  T.dense = c->tab_dense;
+  T.x0 = c->tab_lo[0]; T.y0 = c->tab_lo[1]; T.t0 = c->tab_lo[2];
+  T.ex = c->tab_ext[0]; T.ey = c->tab_ext[1]; T.et = c->tab_ext[2];
+  return T;
+}
+
+// Histogram over the first `count` keys of d_keys: slot per sample, first-
+// occurrence flags.  Chooses the dense grid when the keys' bounding box fits
+// the table, the hash otherwise.
 static void build_histogram(PfCtx *c, int count)
 {
   cudaStream_t st = globals().stream;
-  AMCL_CUDA(cudaMemsetAsync(c->d_hash, 0xFF, sizeof(HashSlot) * (size_t)c->hash_cap, st));
-  hash_insert<<<blocks_for(count, 256), 256, 0, st>>>(c->d_keys, count, c->d_hash,
-                                                      c->hash_cap - 1, c->d_slot);
+  int *h = c->h_ints + I_BOUNDS;
+  for (int q = 0; q < 3; q++) { h[q] = 0x7FFFFFFF; h[3 + q] = -0x7FFFFFFF; }
+  AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_BOUNDS, h, sizeof(int) * 6, cudaMemcpyHostToDevice, st));
+  int grid = globals().sm_count * 8;
+  if (grid > blocks_for(count, 256)) grid = blocks_for(count, 256);
+  key_bounds<<<grid, 256, 0, st>>>(c->d_keys, count, c->d_ints + I_BOUNDS);
   AMCL_LAUNCH_CHECK();
-  mark_first<<<blocks_for(count, 256), 256, 0, st>>>(c->d_hash, c->d_slot, count, c->d_flag);
+  sync_ints(c, I_BOUNDS, 6);
+  double cells = 1.0;
+  for (int q = 0; q < 3; q++)
+  {
+    c->tab_lo[q] = h[q];
+    c->tab_ext[q] = count > 0 ? h[3 + q] - h[q] + 1 : 1;
+    cells *= (double)c->tab_ext[q];
+  }
+  c->tab_dense = (count > 0 && cells <= (double)c->hash_cap) ? 1 : 0;
+  if (c->tab_dense)
+    AMCL_CUDA(cudaMemsetAsync(c->d_tab_first, 0xFF, sizeof(unsigned int) * (size_t)cells, st));
+  else
+  {
+    AMCL_CUDA(cudaMemsetAsync(c->d_tab_key, 0xFF, sizeof(unsigned long long) * (size_t)c->hash_cap, st));
+    AMCL_CUDA(cudaMemsetAsync(c->d_tab_first, 0xFF, sizeof(unsigned int) * (size_t)c->hash_cap, st));
+  }
+  const BinTable T = table_of(c);
+  bin_insert<<<blocks_for(count, 256), 256, 0, st>>>(c->d_keys, count, T, c->d_slot);
+  AMCL_LAUNCH_CHECK();
+  mark_first<<<blocks_for(count, 256), 256, 0, st>>>(c->d_tab_first, c->d_slot, count, c->d_flag);
   AMCL_LAUNCH_CHECK();
 }
 
@@ -818,22 +938,36 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
   unsigned int *cmin = c->d_scan + c->alloc_samples;  // second half: per-slot scratch (hash_cap)
   const int nb = blocks_for(n, 256);
 
-  cc_init<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin);
+  const BinTable T = table_of(c);
+  const unsigned int nslots =
+      T.dense ? (unsigned int)T.ex * (unsigned int)T.ey * (unsigned int)T.et : c->hash_cap;
+  const int sb = (int)((nslots + 255u) / 256u);
+  cc_init<<<sb, 256, 0, st>>>(T, nslots, n, cmin);
   AMCL_LAUNCH_CHECK();
-  cc_link<<<nb, 256, 0, st>>>(c->d_hash, c->hash_cap - 1, c->d_slot, c->d_flag, n);
+  cc_link<<<sb, 256, 0, st>>>(T, nslots, n);
   AMCL_LAUNCH_CHECK();
-  unsigned int *root_tmp = reinterpret_cast<unsigned int *>(c->d_label);  // labels come later
-  cc_roots<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin, root_tmp);
-  AMCL_LAUNCH_CHECK();
-  cc_flatten<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, root_tmp);
+  // flatten: rounds of pointer jumping in groups of four, until a round moves nothing
+  for (int group = 0; group < 16; group++)
+  {
+    AMCL_CUDA(cudaMemsetAsync(c->d_ints + I_MOVED, 0, sizeof(int), st));
+    for (int r = 0; r < 4; r++)
+    {
+      if (r == 3) AMCL_CUDA(cudaMemsetAsync(c->d_ints + I_MOVED, 0, sizeof(int), st));
+      cc_jump<<<sb, 256, 0, st>>>(T, nslots, n, c->d_ints + I_MOVED);
+      AMCL_LAUNCH_CHECK();
+    }
+    sync_ints(c, I_MOVED, 1);
+    if (!c->h_ints[I_MOVED]) break;
+  }
+  cc_component_min<<<sb, 256, 0, st>>>(T, nslots, n, cmin);
   AMCL_LAUNCH_CHECK();
   // cluster-opening flags reuse d_keys' storage as u32 scratch (keys are spent)
   unsigned int *cflag = reinterpret_cast<unsigned int *>(c->d_keys);
   unsigned int *cscan = cflag + c->alloc_samples;
-  cc_mark_cluster_first<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, c->d_flag, n, cmin, cflag);
+  cc_mark_cluster_first<<<nb, 256, 0, st>>>(T, c->d_slot, c->d_flag, n, cmin, cflag);
   AMCL_LAUNCH_CHECK();
   scan_u32(c, cflag, cscan, n, I_CLUSTERS);
-  cc_assign_ids<<<nb, 256, 0, st>>>(c->d_hash, c->d_slot, cflag, cscan, n, cmin);
+  cc_assign_ids<<<nb, 256, 0, st>>>(T, c->d_slot, cflag, cscan, n, cmin);
   AMCL_LAUNCH_CHECK();
   sync_ints(c, I_CLUSTERS, 1);
   const int ncl = c->h_ints[I_CLUSTERS];
@@ -849,7 +983,7 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
     int grid = globals().sm_count * 8;
     const int need = blocks_for(acc_cnt, 256);
     if (grid > need) grid = need;
-    cluster_accumulate<<<grid, 256, 0, st>>>(c->d_set[which], acc_cnt, c->d_hash, c->d_slot, cmin,
+    cluster_accumulate<<<grid, 256, 0, st>>>(c->d_set[which], acc_cnt, c->d_tab_aux, c->d_slot, cmin,
                                              c->d_cluster_acc, c->d_label, acc_lo);
   }
   AMCL_LAUNCH_CHECK();
