@@ -102,8 +102,15 @@ enum { MODE_LF = 0, MODE_LFP = 1, MODE_COUNT = 2 };
 constexpr int kSensorThreads = 256;
 constexpr double kCellGuard = 536870912.0;  // 2^29: beyond this nothing is on a map
 
+// Particles handled together by one warp: every beam-table entry fetched from
+// shared memory is applied to kBlockP particles, which divides the shared-
+// memory traffic of the table by kBlockP and keeps kBlockP independent map
+// gathers in flight per lane (ncu on the one-particle version: L1TEX 75 % busy,
+// half of it beam-table wavefronts; profiles/r1_ncu_full_likelihood_field_2M.md).
+constexpr int kBlockP = 4;
+
 template <int MODE, bool LUT_IN_SMEM>
-__global__ void __launch_bounds__(kSensorThreads)
+__global__ void __launch_bounds__(kSensorThreads, 3)
 likelihood_field_kernel(const LfArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -134,65 +141,83 @@ likelihood_field_kernel(const LfArgs a)
   const int warps_per_block = blockDim.x >> 5;
   const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   const int warp_stride = gridDim.x * warps_per_block;
+  const uint16_t *__restrict__ code = a.code;
+  const int tiles_x = a.tiles_x;
+  const unsigned usx = (unsigned)a.sx, usy = (unsigned)a.sy;
+  const int offmap = a.code_offmap;
   double warp_total = 0.0;  // meaningful in lane 0
 
-  for (int p = warp_global; p < a.n; p += warp_stride)
+  for (int p0 = warp_global * kBlockP; p0 < a.n; p0 += warp_stride * kBlockP)
   {
-    const Particle s = load_particle(a.set + p);
-    // pf_vector_coord_add(laser_pose, pose) (pf_vector.c:106-116); only the
-    // sine and cosine of the summed heading are needed below.
+    // Lane q (< kBlockP) prepares particle p0+q: laser pose by
+    // pf_vector_coord_add(laser_pose, pose) (pf_vector.c:106-116) -- only the
+    // sine / cosine of the summed heading are needed -- and the cell-unit
+    // origin MAP_GXWX / MAP_GYWY (map.h:137-138) with size/2 folded in.
+    const int mine = min(p0 + (lane & (kBlockP - 1)), a.n - 1);
+    const Particle s = load_particle(a.set + mine);
     double sn, cs;
     sincos(s.th, &sn, &cs);
     const double px = s.x + a.lx * cs - a.ly * sn;
     const double py = s.y + a.lx * sn + a.ly * cs;
     double st = sn, ct = cs;
     if (a.la != 0.0) sincos(s.th + a.la, &st, &ct);
-    // MAP_GXWX / MAP_GYWY (map.h:137-138) in cell units, size/2 folded in
     double X0 = (px - a.ox) / a.scale + a.half_x;
     double Y0 = (py - a.oy) / a.scale + a.half_y;
-    const bool sane = fabs(X0) < kCellGuard && fabs(Y0) < kCellGuard;
-    if (!sane) { X0 = -kCellGuard; Y0 = -kCellGuard; st = 0.0; ct = 0.0; }
-
-    double acc0 = 0.0, acc1 = 0.0;
-    for (int i = lane; i < a.nb; i += 64)
+    if (!(fabs(X0) < kCellGuard && fabs(Y0) < kCellGuard))
     {
-      const int i1 = i + 32;
-      const bool has1 = i1 < a.nb;
-      const double2 b0 = s_beams[i];
-      const double2 b1 = s_beams[has1 ? i1 : i];
-      const int mi0 = floor_to_int(fma(ct, b0.x, fma(-st, b0.y, X0)));
-      const int mj0 = floor_to_int(fma(st, b0.x, fma(ct, b0.y, Y0)));
-      const int mi1 = floor_to_int(fma(ct, b1.x, fma(-st, b1.y, X0)));
-      const int mj1 = floor_to_int(fma(st, b1.x, fma(ct, b1.y, Y0)));
-      int c0 = a.code_offmap, c1 = a.code_offmap;
-      if ((unsigned)mi0 < (unsigned)a.sx && (unsigned)mj0 < (unsigned)a.sy)
-        c0 = __ldg(a.code + ((size_t)((mj0 >> 2) * a.tiles_x + (mi0 >> 2)) << 4) +
-                   ((mj0 & 3) << 2) + (mi0 & 3));
-      if ((unsigned)mi1 < (unsigned)a.sx && (unsigned)mj1 < (unsigned)a.sy)
-        c1 = __ldg(a.code + ((size_t)((mj1 >> 2) * a.tiles_x + (mi1 >> 2)) << 4) +
-                   ((mj1 & 3) << 2) + (mi1 & 3));
-      if (MODE == MODE_COUNT)
+      X0 = -kCellGuard; Y0 = -kCellGuard; st = 0.0; ct = 0.0;   // nothing of it is on the map
+    }
+    double pX[kBlockP], pY[kBlockP], pc[kBlockP], ps[kBlockP], pw[kBlockP], acc[kBlockP];
+#pragma unroll
+    for (int q = 0; q < kBlockP; q++)
+    {
+      pX[q] = __shfl_sync(kFullMask, X0, q);
+      pY[q] = __shfl_sync(kFullMask, Y0, q);
+      pc[q] = __shfl_sync(kFullMask, ct, q);
+      ps[q] = __shfl_sync(kFullMask, st, q);
+      pw[q] = __shfl_sync(kFullMask, s.w, q);
+      acc[q] = 0.0;
+    }
+
+    for (int i = lane; i < a.nb; i += 32)
+    {
+      const double2 b = s_beams[i];
+      int c[kBlockP];
+#pragma unroll
+      for (int q = 0; q < kBlockP; q++)
       {
-        if (a.agree[c0]) atomicAdd(&s_counts[i], 1);
-        if (has1 && a.agree[c1]) atomicAdd(&s_counts[i1], 1);
+        const int mi = floor_to_int(fma(pc[q], b.x, fma(-ps[q], b.y, pX[q])));
+        const int mj = floor_to_int(fma(ps[q], b.x, fma(pc[q], b.y, pY[q])));
+        c[q] = offmap;
+        if ((unsigned)mi < usx && (unsigned)mj < usy)
+          c[q] = __ldg(code + ((((mj >> 2) * tiles_x + (mi >> 2)) << 4) | ((mj & 3) << 2) | (mi & 3)));
       }
-      else
+#pragma unroll
+      for (int q = 0; q < kBlockP; q++)
       {
-        acc0 += lut[c0];
-        if (has1) acc1 += lut[c1];
+        if (MODE == MODE_COUNT)
+        {
+          if (p0 + q < a.n && a.agree[c[q]]) atomicAdd(&s_counts[i], 1);
+        }
+        else
+          acc[q] += lut[c[q]];
       }
     }
     if (MODE != MODE_COUNT)
     {
-      const double sum = warp_sum(acc0 + acc1);
-      if (lane == 0)
+#pragma unroll
+      for (int q = 0; q < kBlockP; q++)
       {
-        // LF : p = 1 + sum pz^3          (amcl_laser.cpp:241,295,298)
-        // LFP: weight *= exp(sum log pz)  (amcl_laser.cpp:437,444)
-        const double factor = MODE == MODE_LF ? 1.0 + sum : exp(sum);
-        const double w = s.w * factor;
-        a.set[p].w = w;
-        warp_total += w;
+        const double sum = warp_sum(acc[q]);
+        if (lane == 0 && p0 + q < a.n)
+        {
+          // LF : p = 1 + sum pz^3          (amcl_laser.cpp:241,295,298)
+          // LFP: weight *= exp(sum log pz)  (amcl_laser.cpp:437,444)
+          const double factor = MODE == MODE_LF ? 1.0 + sum : exp(sum);
+          const double w = pw[q] * factor;
+          a.set[p0 + q].w = w;
+          warp_total += w;
+        }
       }
     }
   }
@@ -516,7 +541,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   do                                                                                     \
   {                                                                                      \
     grid = persistent_grid(likelihood_field_kernel<MODE, INSMEM>, kSensorThreads, smem); \
-    int need_blocks = (n + (kSensorThreads / 32) - 1) / (kSensorThreads / 32);           \
+    int need_blocks = (n + (kSensorThreads / 32) * kBlockP - 1) / ((kSensorThreads / 32) * kBlockP); \
     if (grid > need_blocks) grid = need_blocks > 0 ? need_blocks : 1;                    \
     ensure_partials(c, grid);                                                            \
     a.block_totals = c->d_partials;                                                      \
