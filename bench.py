@@ -368,6 +368,9 @@ def b200_arm(args):
            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
            "note": "deferred host mirror; eager mirror adds a %d MB D2H per API call" % ((32 * n_local) >> 20)}
 
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
     line = {
