@@ -154,6 +154,8 @@ unsigned long long amclb200_launch_count(void);
  * and a switch to force the single-thread walk (on = 0). */
 unsigned long long amclb200_cumsum_fallbacks(void);
 void amclb200_set_parallel_cumsum(int on);
+/* out = {tiles that had to be walked element by element, tiles} of the last table. */
+void amclb200_cumsum_last_tiles(int out[2]);
 
 /* out[0] = milliseconds of the laser-model kernel of the last UpdateSensor,
  * out[1] = particle-beam evaluations it performed. */

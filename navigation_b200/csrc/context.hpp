@@ -219,6 +219,7 @@ void run_philox_gaussian_init(PfCtx *c, int which, const double mean[3],
 // exact sequential-order cumulative table (pf.c:399-402) of the weights of a set
 void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum);
 unsigned long long exact_cumsum_fallback_count();
+void exact_cumsum_last_tiles(int out[2]);   // {dirty tiles, tiles} of the last parallel table
 
 struct StageTimer
 {

@@ -43,6 +43,7 @@ constexpr int kTileLen = 1024;
 constexpr int kTileThreads = 256;
 constexpr int kPerThread = kTileLen / kTileThreads;   // 4 consecutive weights per thread
 constexpr int kDirty = -100000;
+constexpr int kFlat = -200000;    // every weight of the tile is exactly 0: the table does not move
 
 struct PairFn
 {
@@ -131,24 +132,40 @@ __device__ PairFn block_scan_fn(PairFn v, PairFn *total, PairFn *s_warp)
 }
 
 // ---- A: fp64 sum of each tile (any fixed order; only used for classification)
-__global__ void cs_tile_sums(const Particle *__restrict__ set, int n, double *__restrict__ tile_sum)
+__global__ void cs_tile_sums(const Particle *__restrict__ set, int n, double *__restrict__ tile_sum,
+                             double *__restrict__ tile_max)
 {
   __shared__ double s_red[32];
   const int base = blockIdx.x * kTileLen;
-  double v = 0.0;
+  double v = 0.0, mx = 0.0;
 #pragma unroll
   for (int k = 0; k < kPerThread; k++)
   {
     const int i = base + k * kTileThreads + threadIdx.x;
-    if (i < n) v += set[i].w;
+    if (i < n)
+    {
+      const double w = set[i].w;
+      v += w;
+      mx = fmax(mx, w);
+    }
   }
   const double t = block_sum(v, s_red);
-  if (threadIdx.x == 0) tile_sum[blockIdx.x] = t;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(kFullMask, mx, o));
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+    for (int k = 1; k < (int)(blockDim.x >> 5); k++) mx = fmax(mx, s_red[k]);
+    tile_sum[blockIdx.x] = t;
+    tile_max[blockIdx.x] = mx;
+  }
 }
 
 // ---- B: rough prefix of the tile sums and clean/dirty classification ---------
-__global__ void cs_classify(const double *__restrict__ tile_sum, int tiles, int n,
-                            int *__restrict__ tile_class)
+__global__ void cs_classify(const double *__restrict__ tile_sum, const double *__restrict__ tile_max,
+                            int tiles, int n, int *__restrict__ tile_class, int *dirty_count)
 {
   __shared__ double s_part[1024];
   __shared__ double s_total;
@@ -171,23 +188,34 @@ __global__ void cs_classify(const double *__restrict__ tile_sum, int tiles, int 
     s_total = run;
   }
   __syncthreads();
-  // |sequential c - any fp64 prefix| <= n * 2^-53 * total for each of the two;
-  // the margin doubles that again.
-  const double total = s_total;
-  const double delta = 4.0 * (double)n * 1.1102230246251565e-16 * total;
+  // Weights are non-negative, so every partial sum -- the sequential one and this
+  // rough prefix alike -- carries a RELATIVE error of at most (#additions) * 2^-53
+  // <= n * 2^-53.  The margin below is four times that, relative to the local
+  // magnitude, so tiles deep in the tiny-weight region (likelihood_field_prob
+  // leaves weights 300 orders of magnitude apart) are still classified exactly.
+  const double eps = 4.0 * (double)n * 1.1102230246251565e-16;
   double run = s_part[threadIdx.x];
   for (int t = lo; t < hi; t++)
   {
-    const double start = run - delta;
+    const double before = run;
+    const double start = run * (1.0 - eps);
     run += tile_sum[t];
-    const double end = run + delta;
+    const double end = run * (1.0 + eps);
     int cls = kDirty;
-    if (start > 0.0 && isfinite(end))
+    (void)before;
+    // Flat: no addition in the tile can move the table.  True when every weight
+    // is 0, and also when the largest weight is below a quarter ulp of the
+    // smallest value the running sum can have here (c + w rounds back to c,
+    // whatever the binade -- the tail of a likelihood_field_prob posterior).
+    if (tile_sum[t] == 0.0 || (start > 0.0 && tile_max[t] < start * 2.7755575615628914e-17))
+      cls = kFlat;
+    else if (start > 0.0 && isfinite(end))
     {
       const int e0 = ilogb(start), e1 = ilogb(end);
-      if (e0 == e1 && e0 > -900 && e0 < 900) cls = e0;
+      if (e0 == e1 && e0 > -1020 && e0 < 1020) cls = e0;
     }
     tile_class[t] = cls;
+    if (cls == kDirty) atomicAdd(dirty_count, 1);
   }
 }
 
@@ -197,7 +225,7 @@ __global__ void cs_tile_fns(const Particle *__restrict__ set, int n, const int *
 {
   __shared__ PairFn s_warp[33];
   const int cls = tile_class[blockIdx.x];
-  if (cls == kDirty) return;                     // uniform across the block
+  if (cls == kDirty || cls == kFlat) return;     // uniform across the block
   const int shift = 52 - cls;
   const int first = blockIdx.x * kTileLen + threadIdx.x * kPerThread;
   PairFn f = fn_identity();
@@ -251,22 +279,49 @@ __global__ void cs_carries(const Particle *__restrict__ set, int n, int tiles,
         for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(kFullMask, v, o));
         if (tid == 0) s_first_dirty = v;
       }
-      if (tid == cursor) s_run_class = cls;
       __syncthreads();
       const int d = s_first_dirty;
-      const int run_end = min(d, tiles - base);          // clean tiles [cursor, run_end)
+      const int run_end = min(d, tiles - base);          // non-dirty tiles [cursor, run_end)
       if (run_end > cursor)
       {
-        const int e = s_run_class;
         const bool in_run = tid >= cursor && tid < run_end;
-        PairFn f = in_run ? tile_fn[t] : fn_identity();
-        PairFn total;
-        const PairFn ex = block_scan_fn(f, &total, s_warp);
-        const unsigned long long C0 = (unsigned long long)scalbn(s_carry, 52 - e);
-        if (in_run) carry_in[t] = scalbn((double)fn_apply(ex, C0), e - 52);
-        __syncthreads();                                  // everyone has read s_carry
-        if (tid == 0) s_carry = scalbn((double)fn_apply(total, C0), e - 52);
+        // The binade of the run is that of its first tile that has weight in it:
+        // flat tiles fit any binade, and a change of binade needs a crossing,
+        // which makes a tile dirty and ends the run.
+        int pick = (in_run && cls != kFlat) ? tid : (int)blockDim.x;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) pick = min(pick, __shfl_xor_sync(kFullMask, pick, o));
+        if ((tid & 31) == 0) s_min[tid >> 5] = pick;
         __syncthreads();
+        if (tid < 32)
+        {
+          int v = tid < (int)(blockDim.x >> 5) ? s_min[tid] : (int)blockDim.x;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(kFullMask, v, o));
+          if (tid == 0) s_first_dirty = v;                // reused as "first non-flat"
+        }
+        __syncthreads();
+        const int first_solid = s_first_dirty;
+        if (tid == first_solid) s_run_class = cls;
+        __syncthreads();
+        if (first_solid >= (int)blockDim.x)
+        {
+          // nothing but flat tiles: the carry passes through untouched
+          if (in_run) carry_in[t] = s_carry;
+          __syncthreads();
+        }
+        else
+        {
+          const int e = s_run_class;
+          PairFn f = (in_run && cls != kFlat) ? tile_fn[t] : fn_identity();
+          PairFn total;
+          const PairFn ex = block_scan_fn(f, &total, s_warp);
+          const unsigned long long C0 = (unsigned long long)scalbn(s_carry, 52 - e);
+          if (in_run) carry_in[t] = scalbn((double)fn_apply(ex, C0), e - 52);
+          __syncthreads();                                  // everyone has read s_carry
+          if (tid == 0) s_carry = scalbn((double)fn_apply(total, C0), e - 52);
+          __syncthreads();
+        }
       }
       if (d >= (int)blockDim.x || base + d >= tiles) break;
       // walk the dirty tile with real fp64 additions
@@ -301,6 +356,16 @@ __global__ void cs_apply(const Particle *__restrict__ set, int n, const int *__r
   __shared__ PairFn s_warp[33];
   const int cls = tile_class[blockIdx.x];
   if (cls == kDirty) return;
+  if (cls == kFlat)
+  {
+    const double v = carry_in[blockIdx.x];
+    for (int k = threadIdx.x; k < kTileLen; k += blockDim.x)
+    {
+      const int i = blockIdx.x * kTileLen + k;
+      if (i < n) cum[i + 1] = v;
+    }
+    return;
+  }
   const int shift = 52 - cls;
   const int first = blockIdx.x * kTileLen + threadIdx.x * kPerThread;
   double w[kPerThread];
@@ -336,10 +401,12 @@ __global__ void cs_verify(const Particle *__restrict__ set, int n, const double 
 }
 
 unsigned long long g_fallbacks = 0;
+int g_last_dirty = 0, g_last_tiles = 0;
 
 }  // namespace
 
 unsigned long long exact_cumsum_fallback_count() { return g_fallbacks; }
+void exact_cumsum_last_tiles(int out[2]) { out[0] = g_last_dirty; out[1] = g_last_tiles; }
 
 void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum)
 {
@@ -355,9 +422,12 @@ void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum)
     AMCL_CUDA(cudaMalloc(&c->d_tile_class, sizeof(int) * (size_t)c->tile_cap));
   }
   PairFn *tile_fn = reinterpret_cast<PairFn *>(c->d_tile_fn);
-  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_sum);
+  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_sum, c->d_tile_carry);
   AMCL_LAUNCH_CHECK();
-  cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, tiles, n, c->d_tile_class);
+  const int bad_slot = 8, dirty_slot = 9;
+  AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, 2 * sizeof(int), st));
+  cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, c->d_tile_carry, tiles, n, c->d_tile_class,
+                                 c->d_ints + dirty_slot);
   AMCL_LAUNCH_CHECK();
   cs_tile_fns<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_class, tile_fn);
   AMCL_LAUNCH_CHECK();
@@ -365,13 +435,13 @@ void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum)
   AMCL_LAUNCH_CHECK();
   cs_apply<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_class, c->d_tile_carry, d_cum);
   AMCL_LAUNCH_CHECK();
-  const int bad_slot = 8;
-  AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, sizeof(int), st));
   cs_verify<<<(n + 255) / 256, 256, 0, st>>>(set, n, d_cum, c->d_ints + bad_slot);
   AMCL_LAUNCH_CHECK();
-  AMCL_CUDA(cudaMemcpyAsync(c->h_ints + bad_slot, c->d_ints + bad_slot, sizeof(int),
+  AMCL_CUDA(cudaMemcpyAsync(c->h_ints + bad_slot, c->d_ints + bad_slot, 2 * sizeof(int),
                             cudaMemcpyDeviceToHost, st));
   AMCL_CUDA(cudaStreamSynchronize(st));
+  g_last_dirty = c->h_ints[dirty_slot];
+  g_last_tiles = tiles;
   if (c->h_ints[bad_slot])
   {
     g_fallbacks++;

@@ -215,6 +215,9 @@ unsigned long long amclb200_launch_count(void) { return amcl_launch_counter(); }
 // How often the exact cumulative table had to fall back to the single-thread walk.
 unsigned long long amclb200_cumsum_fallbacks(void) { return exact_cumsum_fallback_count(); }
 
+// out = {tiles walked sequentially, tiles} of the last tile-parallel table
+void amclb200_cumsum_last_tiles(int out[2]) { exact_cumsum_last_tiles(out); }
+
 // 1: tile-parallel exact table for large sets (default); 0: always the single-thread walk.
 void amclb200_set_parallel_cumsum(int on) { globals().exact_cumsum_parallel = on != 0; }
 

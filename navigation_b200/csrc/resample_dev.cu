@@ -390,7 +390,9 @@ __global__ void bin_insert(const unsigned long long *__restrict__ keys, int n, c
     unpack_key(key, &kx, &ky, &kt);
     const unsigned int cell =
         (unsigned int)(((kt - T.t0) * T.ey + (ky - T.y0)) * T.ex + (kx - T.x0));
-    atomicMin(&T.first[cell], (unsigned int)m);
+    // converged clouds put millions of samples into a handful of cells: look
+    // first, and only issue the atomic when this sample can lower the value
+    if ((unsigned int)m < __ldcg(&T.first[cell])) atomicMin(&T.first[cell], (unsigned int)m);
     slot_of[m] = cell;
     return;
   }
@@ -400,7 +402,7 @@ __global__ void bin_insert(const unsigned long long *__restrict__ keys, int n, c
     const unsigned long long prev = atomicCAS(&T.key[h], kEmptyKey, key);
     if (prev == kEmptyKey || prev == key)
     {
-      atomicMin(&T.first[h], (unsigned int)m);
+      if ((unsigned int)m < __ldcg(&T.first[h])) atomicMin(&T.first[h], (unsigned int)m);
       slot_of[m] = h;
       return;
     }
@@ -451,6 +453,7 @@ __global__ void find_kld_cut(const unsigned int *__restrict__ k_inclusive, int c
   // limit() only changes where k changes, but evaluating it everywhere keeps
   // the kernel branch-free; min_samples gives a cheap early reject.
   if (m + 1 <= min_samples) return;
+  if (m + 1 >= __ldcg(cut)) return;   // cannot lower the cut: skip the formula and the atomic
   if (m + 1 > resample_limit(k, min_samples, max_samples, pop_err, pop_z)) atomicMin(cut, m + 1);
 }
 

@@ -39,6 +39,7 @@ EXTENSION_SYMBOLS = {
     "amclb200_pf_best_cluster": (C.c_int, [abi.pf_p, abi.c_double_p, C.POINTER(abi.pf_vector_t), C.POINTER(abi.pf_matrix_t)]),
     "amclb200_cumsum_fallbacks": (C.c_uint64, []),
     "amclb200_set_parallel_cumsum": (None, [C.c_int]),
+    "amclb200_cumsum_last_tiles": (None, [C.POINTER(C.c_int)]),
     "amclb200_pf_sensor_kernel_stats": (None, [abi.pf_p, C.POINTER(C.c_double)]),
     "amclb200_measure_gather_rate": (C.c_double, [C.c_uint64, C.c_int]),
     "amclb200_edt_codes_static": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),

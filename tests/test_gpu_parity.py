@@ -350,6 +350,11 @@ def _weights(kind, n, seed):
     elif kind == "tiny":                    # LFP-like: almost all weight on a few particles
         w = np.exp(-rng.uniform(0, 700, size=n))
         w[n // 3] = 1.0
+    elif kind == "underflow":               # likelihood_field_prob: exact zeros, denormals, 600 decades
+        w = np.exp(-rng.uniform(0, 1500, size=n))
+        w[: n // 5] = 0.0                    # a long run of leading zeros
+        w[n // 2] = 1.0
+        return w / w.sum()
     elif kind == "posterior":               # what a sensor update leaves behind
         w = (1.0 + rng.gamma(2.0, size=n) * 50.0)
     w = w / w.sum()
@@ -360,7 +365,8 @@ def _weights(kind, n, seed):
 
 @pytest.mark.parametrize("kind,n,seed", [("gamma", 5000, 1), ("gamma", 70000, 2), ("uniform", 300001, 3),
                                          ("dyadic", 200000, 4), ("tiny", 150000, 5),
-                                         ("posterior", 2500000, 6), ("gamma", 16384, 7)])
+                                         ("posterior", 2500000, 6), ("gamma", 16384, 7),
+                                         ("underflow", 1500000, 8)])
 def test_cumulative_table_bit_exact(lib, port, kind, n, seed):
     """C5: the table must be the SEQUENTIAL fp64 running sum, bit for bit -- for
     the single-thread walk (small n) and the tile-parallel exact scan (large n)."""
