@@ -477,3 +477,78 @@ def test_full_update_loop_tracks_reference(lib, ref):
     assert a["n"] == b["n"] and a["k"] == b["k"]
     assert np.allclose(a["mean"], b["mean"], rtol=1e-6, atol=1e-7)
     assert rel_err(b["samples"][:, :3], a["samples"][:, :3], floor=1e-6) < RTOL
+
+
+# ------------------------------------------------- full-size property checks ----
+
+def test_k3_full_size_edt_bit_exact(lib, port):
+    """BASELINE config 3: 4000 x 4000 map at 0.05 m, max_occ_dist 2.0 -- every
+    cell equals the oracle's exact transform."""
+    occ = synth.rooms_map(4000, seed=1)
+    side = Side(lib, occ)
+    side.update_cspace(2.0)
+    got = side.occ_dist()
+    want = oracle.occ_dist_from_d2(oracle.edt_exact(occ, 40), 0.05, 2.0)
+    assert np.array_equal(got, want)
+    side.close()
+
+
+def test_k4_full_size_resample_properties(lib, port):
+    """4 Mi particles, likelihood_field_prob, 1080 beams, then KLD resample:
+    checked through properties that do not need an O(N^2) oracle run --
+    normalisation, the table recurrence, source/pose consistency, the distinct-
+    bin count and the KLD stopping rule recomputed on the host from the keys."""
+    lib.amclb200_set_rng(library.RNG_PHILOX, 99)
+    size, n, beams = 4000, 1 << 22, 1080
+    occ = synth.rooms_map(size, seed=1)
+    side = Side(lib, occ)
+    side.alloc(100, n)
+    lib.amclb200_set_mirror(side.pf, 0)
+    side.make_laser(beams, model="lfp")
+    pose = synth.room_centre_pose(size, 0.05)
+    bear = synth.scan_bearings(beams)
+    rays = np.stack([np.full_like(bear, pose[0]), np.full_like(bear, pose[1]), pose[2] + bear], 1).copy()
+    rng = np.empty(beams)
+    lib.amclb200_map_calc_ranges(side.map, rays.ctypes.data, beams, 30.0, rng.ctypes.data)
+    scan = np.stack([np.minimum(rng, 30.0), bear], 1).copy()
+    cloud = synth.gaussian_cloud(pose, (0.5, 0.5, 0.26), n, 3)
+    side.set_samples(cloud)
+    side.update_sensor(scan, 30.0)
+    before = side.samples()
+    assert abs(before[:, 3].sum() - 1.0) < 1e-9
+    assert np.array_equal(before[:, :3], cloud[:, :3])
+    # the table: exact recurrence, no fallback
+    fb = lib.amclb200_cumsum_fallbacks()
+    cum = np.empty(n + 1)
+    lib.amclb200_pf_cumulative_table(side.pf, cum.ctypes.data, n + 1)
+    assert lib.amclb200_cumsum_fallbacks() == fb
+    want = np.empty(n + 1)
+    port.orc_cumsum(before, n, want)
+    assert np.array_equal(cum, want)
+    side.resample()
+    after = side.samples()
+    cnt = after.shape[0]
+    src = np.empty(n, np.int32)
+    assert lib.amclb200_pf_resample_sources(side.pf, src.ctypes.data, n) == cnt
+    assert np.all((src[:cnt] >= 0) & (src[:cnt] < n))
+    assert np.all(before[src[:cnt], 3] > 0)                         # pf.c:470
+    assert np.array_equal(after[:, :3], before[src[:cnt], :3])      # poses are copies
+    assert np.all(after[:, 3] == 1.0 / cnt)
+    # distinct bins and the stopping rule, recomputed on the host
+    keys = np.floor(after[:, :3] / np.array([0.5, 0.5, 10 * np.pi / 180])).astype(np.int64)
+    flat = (keys[:, 0] + (1 << 20)) << 43 | (keys[:, 1] + (1 << 20)) << 22 | (keys[:, 2] + (1 << 21))
+    _, first = np.unique(flat, return_index=True)
+    assert side.cur.kdtree.contents.leaf_count == first.size
+    is_first = np.zeros(cnt, np.int64)
+    is_first[first] = 1
+    k_m = np.cumsum(is_first)
+    if cnt < n:
+        lim = port.orc_resample_limit(int(k_m[cnt - 1]), 100, n, 0.01, 0.99)
+        assert cnt > lim                                            # stopped here ...
+        for m in range(max(0, cnt - 50), cnt - 1):                  # ... and not earlier
+            assert m + 1 <= port.orc_resample_limit(int(k_m[m]), 100, n, 0.01, 0.99)
+    tab = side.cluster_table()
+    assert abs(sum(t[0] for t in tab) - 1.0) < 1e-9
+    assert sum(side.cur.clusters[c].count for c in range(len(tab))) == cnt
+    lib.amclb200_set_rng(library.RNG_DRAND48, 0)
+    side.close()
