@@ -141,6 +141,11 @@ typedef void (*amclb200_allgather_fn)(void *d_buf, unsigned long long bytes_per_
  * keys before resampling, per-cluster sums).  Results equal the one-GPU run. */
 void amclb200_pf_set_shard(pf_t *pf, int rank, int world, amclb200_allreduce_fn allreduce,
                            amclb200_allgather_fn allgather, void *user);
+/* Collective, optional, once after amclb200_pf_set_shard: map every rank's particle
+ * arrays into this process (CUDA IPC).  pf_update_resample then all-gathers only
+ * the 8-byte weights and reads the poses it picks from their owners' memory over
+ * NVLink inside the pick kernel, instead of all-gathering the whole 32-byte set. */
+void amclb200_pf_enable_peer_access(pf_t *pf);
 /* Device-to-device load of this rank's slice of an n_global-particle cloud. */
 void amclb200_pf_load_device_shard(pf_t *pf, const void *d_slice, int n_global);
 /* out = [lo, hi): the slice of a set of n particles this rank owns. */

@@ -117,6 +117,12 @@ struct PfCtx
   int alloc_samples = 0;          // max_samples padded so world*chunk always fits
   Shard shard;
   bool replicated[2] = {true, true};  // whole set valid on this rank (not only the owned slice)
+  // peer-memory path: every rank's particle arrays mapped into this process (CUDA IPC
+  // over NVLink); d_peer_tab[j][r] = rank r's array for set j, as seen from this GPU
+  bool peers_ready = false;
+  const Particle **d_peer_tab[2] = {nullptr, nullptr};
+  std::vector<void *> peer_opened;
+  double *d_wpack = nullptr;      // packed weights of the whole set (sharded resample)
   Particle *d_set[2] = {nullptr, nullptr};
   bool mirror_eager = true;       // D2H the sample array after every update
   bool host_fresh[2] = {false, false};
@@ -175,6 +181,7 @@ struct PfCtx
 
 PfCtx *pf_ctx(pf_t *pf);                       // aborts if unknown
 void pf_replicate(PfCtx *c, int which);        // all-gather the owned slices if needed
+void pf_enable_peers(PfCtx *c);                // collective: map every rank's arrays (CUDA IPC)
 PfCtx *pf_ctx_of_set(pf_sample_set_t *set, int *which);
 PfCtx *pf_ctx_create(pf_t *pf);
 void pf_ctx_release(pf_t *pf);
@@ -215,6 +222,25 @@ void run_cep_stats(PfCtx *c, int which, double out[4]);   // mn, mx, my, mrr
 void run_copy_set(PfCtx *c, int from, int to);
 void run_philox_gaussian_init(PfCtx *c, int which, const double mean[3],
                               const double cr[9], const double cd[3]);
+
+// A strided view of weights: the w field of an AoS particle array (stride 4
+// doubles) or a packed array (stride 1).
+struct Weights
+{
+  const double *p;
+  int stride;
+#ifdef __CUDACC__
+  __device__ __forceinline__ double operator[](int i) const { return p[(size_t)i * stride]; }
+#endif
+};
+inline Weights weights_of(const Particle *set)
+{
+  Weights w;
+  w.p = reinterpret_cast<const double *>(set) + 3;
+  w.stride = 4;
+  return w;
+}
+void exact_cumsum_w(PfCtx *c, Weights w, int n, double *d_cum);
 
 // exact sequential-order cumulative table (pf.c:399-402) of the weights of a set
 void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum);

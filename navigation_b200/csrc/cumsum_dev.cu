@@ -34,7 +34,7 @@
 namespace amclb200
 {
 
-void launch_cumsum_sequential(const Particle *set, int n, double *d_cum);   // resample_dev.cu
+void launch_cumsum_sequential(Weights W, int n, double *d_cum);   // resample_dev.cu
 
 namespace
 {
@@ -132,7 +132,7 @@ __device__ PairFn block_scan_fn(PairFn v, PairFn *total, PairFn *s_warp)
 }
 
 // ---- A: fp64 sum of each tile (any fixed order; only used for classification)
-__global__ void cs_tile_sums(const Particle *__restrict__ set, int n, double *__restrict__ tile_sum,
+__global__ void cs_tile_sums(const Weights W, int n, double *__restrict__ tile_sum,
                              double *__restrict__ tile_max)
 {
   __shared__ double s_red[32];
@@ -144,7 +144,7 @@ __global__ void cs_tile_sums(const Particle *__restrict__ set, int n, double *__
     const int i = base + k * kTileThreads + threadIdx.x;
     if (i < n)
     {
-      const double w = set[i].w;
+      const double w = W[i];
       v += w;
       mx = fmax(mx, w);
     }
@@ -220,7 +220,7 @@ __global__ void cs_classify(const double *__restrict__ tile_sum, const double *_
 }
 
 // ---- C: composed function of every clean tile ----------------------------------
-__global__ void cs_tile_fns(const Particle *__restrict__ set, int n, const int *__restrict__ tile_class,
+__global__ void cs_tile_fns(const Weights W, int n, const int *__restrict__ tile_class,
                             PairFn *__restrict__ tile_fn)
 {
   __shared__ PairFn s_warp[33];
@@ -233,7 +233,7 @@ __global__ void cs_tile_fns(const Particle *__restrict__ set, int n, const int *
   for (int k = 0; k < kPerThread; k++)
   {
     const int i = first + k;
-    if (i < n) f = fn_compose(f, fn_of_weight(set[i].w, shift));
+    if (i < n) f = fn_compose(f, fn_of_weight(W[i], shift));
   }
   PairFn total;
   block_scan_fn(f, &total, s_warp);
@@ -241,7 +241,7 @@ __global__ void cs_tile_fns(const Particle *__restrict__ set, int n, const int *
 }
 
 // ---- D: exact carry into every tile; dirty tiles are walked here ---------------
-__global__ void cs_carries(const Particle *__restrict__ set, int n, int tiles,
+__global__ void cs_carries(const Weights W, int n, int tiles,
                            const int *__restrict__ tile_class, const PairFn *__restrict__ tile_fn,
                            double *__restrict__ carry_in, double *__restrict__ cum)
 {
@@ -328,7 +328,7 @@ __global__ void cs_carries(const Particle *__restrict__ set, int n, int tiles,
       const int tt = base + d;
       const int a = tt * kTileLen;
       const int m = min(kTileLen, n - a);
-      for (int k = tid; k < m; k += blockDim.x) s_w[k] = set[a + k].w;
+      for (int k = tid; k < m; k += blockDim.x) s_w[k] = W[a + k];
       __syncthreads();
       if (tid == 0)
       {
@@ -350,7 +350,7 @@ __global__ void cs_carries(const Particle *__restrict__ set, int n, int tiles,
 }
 
 // ---- E: per-element table of the clean tiles ----------------------------------------
-__global__ void cs_apply(const Particle *__restrict__ set, int n, const int *__restrict__ tile_class,
+__global__ void cs_apply(const Weights W, int n, const int *__restrict__ tile_class,
                          const double *__restrict__ carry_in, double *__restrict__ cum)
 {
   __shared__ PairFn s_warp[33];
@@ -374,7 +374,7 @@ __global__ void cs_apply(const Particle *__restrict__ set, int n, const int *__r
   for (int k = 0; k < kPerThread; k++)
   {
     const int i = first + k;
-    w[k] = i < n ? set[i].w : 0.0;
+    w[k] = i < n ? W[i] : 0.0;
     f = fn_compose(f, fn_of_weight(w[k], shift));
   }
   PairFn total;
@@ -391,12 +391,12 @@ __global__ void cs_apply(const Particle *__restrict__ set, int n, const int *__r
 }
 
 // ---- F: the defining recurrence, checked everywhere -------------------------------------
-__global__ void cs_verify(const Particle *__restrict__ set, int n, const double *__restrict__ cum,
+__global__ void cs_verify(const Weights W, int n, const double *__restrict__ cum,
                           int *bad)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const double want = __dadd_rn(cum[i], set[i].w);
+  const double want = __dadd_rn(cum[i], W[i]);
   if (!(cum[i + 1] == want) || (i == 0 && cum[0] != 0.0)) *bad = 1;
 }
 
@@ -408,7 +408,7 @@ int g_last_dirty = 0, g_last_tiles = 0;
 unsigned long long exact_cumsum_fallback_count() { return g_fallbacks; }
 void exact_cumsum_last_tiles(int out[2]) { out[0] = g_last_dirty; out[1] = g_last_tiles; }
 
-void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum)
+void exact_cumsum_parallel(PfCtx *c, Weights W, int n, double *d_cum)
 {
   cudaStream_t st = globals().stream;
   const int tiles = (n + kTileLen - 1) / kTileLen;
@@ -422,20 +422,20 @@ void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum)
     AMCL_CUDA(cudaMalloc(&c->d_tile_class, sizeof(int) * (size_t)c->tile_cap));
   }
   PairFn *tile_fn = reinterpret_cast<PairFn *>(c->d_tile_fn);
-  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_sum, c->d_tile_carry);
+  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_carry);
   AMCL_LAUNCH_CHECK();
   const int bad_slot = 8, dirty_slot = 9;
   AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, 2 * sizeof(int), st));
   cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, c->d_tile_carry, tiles, n, c->d_tile_class,
                                  c->d_ints + dirty_slot);
   AMCL_LAUNCH_CHECK();
-  cs_tile_fns<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_class, tile_fn);
+  cs_tile_fns<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_class, tile_fn);
   AMCL_LAUNCH_CHECK();
-  cs_carries<<<1, 1024, 0, st>>>(set, n, tiles, c->d_tile_class, tile_fn, c->d_tile_carry, d_cum);
+  cs_carries<<<1, 1024, 0, st>>>(W, n, tiles, c->d_tile_class, tile_fn, c->d_tile_carry, d_cum);
   AMCL_LAUNCH_CHECK();
-  cs_apply<<<tiles, kTileThreads, 0, st>>>(set, n, c->d_tile_class, c->d_tile_carry, d_cum);
+  cs_apply<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_class, c->d_tile_carry, d_cum);
   AMCL_LAUNCH_CHECK();
-  cs_verify<<<(n + 255) / 256, 256, 0, st>>>(set, n, d_cum, c->d_ints + bad_slot);
+  cs_verify<<<(n + 255) / 256, 256, 0, st>>>(W, n, d_cum, c->d_ints + bad_slot);
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaMemcpyAsync(c->h_ints + bad_slot, c->d_ints + bad_slot, 2 * sizeof(int),
                             cudaMemcpyDeviceToHost, st));
@@ -447,7 +447,7 @@ void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum)
     g_fallbacks++;
     fprintf(stderr, "[amcl_b200] exact_cumsum: recurrence check failed (non-finite or negative "
                     "weights?); using the single-thread walk\n");
-    launch_cumsum_sequential(set, n, d_cum);
+    launch_cumsum_sequential(W, n, d_cum);
   }
 }
 

@@ -186,6 +186,12 @@ void amclb200_pf_set_shard(pf_t *pf, int rank, int world, shard_allreduce_fn all
   c->shard.user = user;
 }
 
+// Collective (every rank calls it once, after amclb200_pf_set_shard): maps every
+// rank's particle arrays into this process with CUDA IPC so that resampling can
+// read the poses it picks straight from their owners over NVLink instead of
+// all-gathering the whole set.
+void amclb200_pf_enable_peer_access(pf_t *pf) { pf_enable_peers(pf_ctx(pf)); }
+
 // Loads THIS RANK'S slice of a cloud of n_global particles from a device array
 // holding just that slice (ceil(n_global/world) records or fewer for the last rank).
 void amclb200_pf_load_device_shard(pf_t *pf, const void *d_slice, int n_global)

@@ -101,6 +101,9 @@ void pf_ctx_release(pf_t *pf)
   PfCtx *c = it->second;
   for (int j = 0; j < 2; j++) cudaFree(c->d_set[j]);
   if (c->d_motion_draws) cudaFree(c->d_motion_draws);
+  for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
+  for (int j = 0; j < 2; j++) if (c->d_peer_tab[j]) cudaFree((void *)c->d_peer_tab[j]);
+  if (c->d_wpack) cudaFree(c->d_wpack);
   cudaFree(c->d_cum); cudaFree(c->d_draws); cudaFree(c->d_src); cudaFree(c->d_label);
   cudaFree(c->d_keys); cudaFree(c->d_slot); cudaFree(c->d_flag); cudaFree(c->d_scan);
   cudaFree(c->d_scan_tiles); cudaFree(c->d_tab_key); cudaFree(c->d_tab_first); cudaFree(c->d_tab_aux); cudaFree(c->d_scalars); cudaFree(c->d_ints);
@@ -126,6 +129,50 @@ void pf_replicate(PfCtx *c, int which)
     c->shard.allgather(c->d_set[which],
                        (unsigned long long)c->shard.chunk(n) * sizeof(Particle), c->shard.user);
   c->replicated[which] = true;
+}
+
+// Exchange CUDA IPC handles of the two particle arrays through the host-supplied
+// all-gather and open every peer's arrays, so that kernels can read remote
+// particles directly over NVLink (resample_dev.cu, pick_and_copy).
+void pf_enable_peers(PfCtx *c)
+{
+  const Shard &sh = c->shard;
+  if (!sh.on() || c->peers_ready) return;
+  cudaStream_t st = globals().stream;
+  const size_t per_rank = 2 * sizeof(cudaIpcMemHandle_t);   // 128 bytes
+  unsigned char *d_stage = nullptr;
+  AMCL_CUDA(cudaMalloc(&d_stage, per_rank * (size_t)sh.world));
+  cudaIpcMemHandle_t mine[2];
+  for (int j = 0; j < 2; j++) AMCL_CUDA(cudaIpcGetMemHandle(&mine[j], c->d_set[j]));
+  AMCL_CUDA(cudaMemcpyAsync(d_stage + per_rank * (size_t)sh.rank, mine, per_rank,
+                            cudaMemcpyHostToDevice, st));
+  AMCL_CUDA(cudaStreamSynchronize(st));
+  sh.allgather(d_stage, per_rank, sh.user);
+  std::vector<cudaIpcMemHandle_t> all((size_t)2 * sh.world);
+  AMCL_CUDA(cudaMemcpyAsync(all.data(), d_stage, per_rank * (size_t)sh.world, cudaMemcpyDeviceToHost, st));
+  AMCL_CUDA(cudaStreamSynchronize(st));
+  cudaFree(d_stage);
+  for (int j = 0; j < 2; j++)
+  {
+    std::vector<const Particle *> tab((size_t)sh.world);
+    for (int r = 0; r < sh.world; r++)
+    {
+      if (r == sh.rank)
+      {
+        tab[r] = c->d_set[j];
+        continue;
+      }
+      void *ptr = nullptr;
+      AMCL_CUDA(cudaIpcOpenMemHandle(&ptr, all[(size_t)2 * r + j], cudaIpcMemLazyEnablePeerAccess));
+      c->peer_opened.push_back(ptr);
+      tab[r] = reinterpret_cast<const Particle *>(ptr);
+    }
+    AMCL_CUDA(cudaMalloc((void **)&c->d_peer_tab[j], sizeof(Particle *) * (size_t)sh.world));
+    AMCL_CUDA(cudaMemcpy((void *)c->d_peer_tab[j], tab.data(), sizeof(Particle *) * (size_t)sh.world,
+                         cudaMemcpyHostToDevice));
+  }
+  AMCL_CUDA(cudaMalloc(&c->d_wpack, sizeof(double) * (size_t)c->alloc_samples));
+  c->peers_ready = true;
 }
 
 void pf_pull(PfCtx *c, int which)

@@ -203,7 +203,7 @@ static void scan_u32(PfCtx *c, const unsigned int *in, unsigned int *out, int n,
 // for large N; see exact_cumsum_parallel.cu when present.)
 constexpr int kSeqChunk = 4096;
 
-__global__ void cumsum_sequential(const Particle *__restrict__ set, int n, double *__restrict__ c)
+__global__ void cumsum_sequential(const Weights W, int n, double *__restrict__ c)
 {
   __shared__ double s_w[kSeqChunk];
   __shared__ double s_carry;
@@ -216,7 +216,7 @@ __global__ void cumsum_sequential(const Particle *__restrict__ set, int n, doubl
   for (int base = 0; base < n; base += kSeqChunk)
   {
     const int m = min(kSeqChunk, n - base);
-    for (int k = threadIdx.x; k < m; k += blockDim.x) s_w[k] = set[base + k].w;
+    for (int k = threadIdx.x; k < m; k += blockDim.x) s_w[k] = W[base + k];
     __syncthreads();
     if (threadIdx.x == 0)
     {
@@ -234,20 +234,25 @@ __global__ void cumsum_sequential(const Particle *__restrict__ set, int n, doubl
   }
 }
 
-void exact_cumsum_parallel(PfCtx *c, const Particle *set, int n, double *d_cum);  // cumsum_dev.cu
+void exact_cumsum_parallel(PfCtx *c, Weights W, int n, double *d_cum);  // cumsum_dev.cu
 
-void launch_cumsum_sequential(const Particle *set, int n, double *d_cum)
+void launch_cumsum_sequential(Weights W, int n, double *d_cum)
 {
-  cumsum_sequential<<<1, 256, 0, globals().stream>>>(set, n, d_cum);
+  cumsum_sequential<<<1, 256, 0, globals().stream>>>(W, n, d_cum);
   AMCL_LAUNCH_CHECK();
+}
+
+void exact_cumsum_w(PfCtx *c, Weights W, int n, double *d_cum)
+{
+  if (globals().exact_cumsum_parallel && n >= 16384)
+    exact_cumsum_parallel(c, W, n, d_cum);
+  else
+    launch_cumsum_sequential(W, n, d_cum);
 }
 
 void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum)
 {
-  if (globals().exact_cumsum_parallel && n >= 16384)
-    exact_cumsum_parallel(c, set, n, d_cum);
-  else
-    launch_cumsum_sequential(set, n, d_cum);
+  exact_cumsum_w(c, weights_of(set), n, d_cum);
 }
 
 // ------------------------------------------------------- draw + search + copy --
@@ -272,6 +277,8 @@ struct PickArgs
   Particle *dst;
   int *src_index;
   unsigned long long *keys;
+  const Particle *const *peers;  // sharded + peer memory: rank r's array of the source set
+  int peer_chunk;           // particles per rank slice (owner of source i = i / peer_chunk)
   int first;                // first candidate index handled by this launch
   int count;                // number of candidates handled
   int write_keys;           // 0: poses only (re-pick after the cut)
@@ -302,12 +309,20 @@ __global__ void pick_and_copy(const PickArgs a)
     }
     if (lo >= a.n_src) lo = a.n_src - 1;  // r beyond the table's last entry
     from = lo;
-    s = load_particle(a.src + lo);
+    // the owner's copy is the current one; a remote owner is read over NVLink
+    const Particle *base = a.peers ? a.peers[lo / a.peer_chunk] : a.src;
+    s = load_particle(base + lo);
   }
   s.w = 1.0;
   store_particle(a.dst + m, s);
   a.src_index[m] = from;
   if (a.write_keys) a.keys[m] = pose_key(s, a.bin_x, a.bin_y, a.bin_t);
+}
+
+__global__ void pack_weights(const Particle *__restrict__ set, int n, double *__restrict__ out)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = set[i].w;
 }
 
 __global__ void keys_of_set(const Particle *__restrict__ set, int n, unsigned long long *keys,
@@ -1155,9 +1170,16 @@ void run_resample(PfCtx *c)
   const int maxs = pf->max_samples;
   const Shard &sh = c->shard;
 
-  // Draws range over the GLOBAL table: a sharded run
-  // first makes the whole source set present on every rank.
-  pf_replicate(c, ia);
+  // Draws range over the GLOBAL table.  A sharded run
+  // needs every weight for the table and any particle's pose for the copy:
+  //  * peer-memory path: all-gather the 8-byte weights only, and let the pick
+  //    kernel read the chosen poses from their owners' memory over NVLink
+  //    (2 x 32 B per output sample instead of shipping the whole set);
+  //  * otherwise: all-gather the whole source set in place.
+  const bool selective_copy =
+      pf->selective_resampling != 0 && set_a->n_effective > 0.5 * (set_a->sample_count);
+  const bool p2p = sh.on() && c->peers_ready && !c->replicated[ia] && !selective_copy;
+  if (!p2p) pf_replicate(c, ia);
 
   // pf.c:378-394
   if (pf->selective_resampling != 0 && set_a->n_effective > 0.5 * (set_a->sample_count))
@@ -1168,7 +1190,23 @@ void run_resample(PfCtx *c)
     return;
   }
 
-  exact_cumsum(c, c->d_set[ia], n_a, c->d_cum);
+  if (p2p)
+  {
+    const int lo = sh.lo(n_a), cnt = sh.count(n_a);
+    if (cnt > 0)
+    {
+      pack_weights<<<blocks_for(cnt, 256), 256, 0, st>>>(c->d_set[ia] + lo, cnt, c->d_wpack + lo);
+      AMCL_LAUNCH_CHECK();
+    }
+    // also the rendezvous that makes every rank's slice final before anyone reads it
+    sh.allgather(c->d_wpack, (unsigned long long)sh.chunk(n_a) * sizeof(double), sh.user);
+    Weights W;
+    W.p = c->d_wpack;
+    W.stride = 1;
+    exact_cumsum_w(c, W, n_a, c->d_cum);
+  }
+  else
+    exact_cumsum(c, c->d_set[ia], n_a, c->d_cum);
 
   // pf.c:411-413
   double w_diff = 1.0 - pf->w_fast / pf->w_slow;
@@ -1247,6 +1285,8 @@ void run_resample(PfCtx *c)
   // ---- pick sources, copy poses, bin keys -----------------------------------
   PickArgs pa;
   pa.src = c->d_set[ia];
+  pa.peers = p2p ? c->d_peer_tab[ia] : nullptr;
+  pa.peer_chunk = sh.chunk(n_a) > 0 ? sh.chunk(n_a) : 1;
   pa.n_src = n_a;
   pa.cum = c->d_cum;
   pa.draws = c->d_draws;

@@ -97,7 +97,11 @@ class Collectives:
     def allgather(self, ptr, bytes_per_rank):
         self._allgather(ptr, bytes_per_rank, None)
 
-    def attach(self, lib, pf):
-        """Make `pf` this rank's shard of a world-wide filter."""
+    def attach(self, lib, pf, peer_access=True):
+        """Make `pf` this rank's shard of a world-wide filter.  With peer_access
+        (GPU only) every rank's particle arrays are mapped into every process, so
+        resampling reads picked poses over NVLink instead of all-gathering them."""
         lib.amclb200_pf_set_shard(pf, self.rank, self.world,
                                   C.cast(self._ar, C.c_void_p), C.cast(self._ag, C.c_void_p), None)
+        if peer_access and self.on_gpu and self.world > 1:
+            lib.amclb200_pf_enable_peer_access(pf)

@@ -53,7 +53,7 @@ def main():
         cloud[: n // 3] = synth.gaussian_cloud(pose, (0.4, 0.4, 0.2), n // 3, 5)
         cloud[:, 3] = 1.0 / n
         if mode == "sharded":
-            coll.attach(lib, side.pf)
+            coll.attach(lib, side.pf, peer_access=os.environ.get("SHARD_P2P", "1") == "1")
         side.set_samples(cloud)            # replicated start on every rank
         log = []
         for step in range(3):
