@@ -10,6 +10,7 @@
 #pragma once
 
 #include <stdint.h>
+#include <utility>
 #include <vector>
 
 #include "amcl/map/map.h"
@@ -246,6 +247,17 @@ void exact_cumsum_w(PfCtx *c, Weights w, int n, double *d_cum);
 void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum);
 unsigned long long exact_cumsum_fallback_count();
 void exact_cumsum_last_tiles(int out[2]);   // {dirty tiles, tiles} of the last parallel table
+
+// Optional stage trace (AMCLB200_TRACE=1): CUDA-event marks inside a call, printed as
+// a one-line breakdown when the call ends.  Off by default; costs nothing then.
+struct Trace
+{
+  std::vector<std::pair<const char *, cudaEvent_t> > marks;
+  bool on;
+  Trace();
+  void mark(const char *name);
+  void report(const char *what);
+};
 
 struct StageTimer
 {

@@ -48,6 +48,39 @@ void ensure_device()
   g.sm_count = prop.multiProcessorCount;
 }
 
+Trace::Trace()
+{
+  const char *e = getenv("AMCLB200_TRACE");
+  on = e && e[0] == '1';
+}
+
+void Trace::mark(const char *name)
+{
+  if (!on) return;
+  cudaEvent_t ev;
+  AMCL_CUDA(cudaEventCreate(&ev));
+  AMCL_CUDA(cudaEventRecord(ev, globals().stream));
+  marks.push_back(std::make_pair(name, ev));
+}
+
+void Trace::report(const char *what)
+{
+  if (!on || marks.size() < 2) return;
+  AMCL_CUDA(cudaEventSynchronize(marks.back().second));
+  fprintf(stderr, "[amcl_b200 trace] %s:", what);
+  for (size_t k = 1; k < marks.size(); k++)
+  {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, marks[k - 1].second, marks[k].second);
+    fprintf(stderr, " %s=%.3f", marks[k].first, ms);
+  }
+  float tot = 0;
+  cudaEventElapsedTime(&tot, marks.front().second, marks.back().second);
+  fprintf(stderr, " total=%.3f ms\n", tot);
+  for (auto &m : marks) cudaEventDestroy(m.second);
+  marks.clear();
+}
+
 StageTimer::StageTimer(float *dst) : out(dst)
 {
   AMCL_CUDA(cudaEventCreate(&a));

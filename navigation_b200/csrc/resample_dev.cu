@@ -266,8 +266,19 @@ __global__ void philox_resample_draws(double *draws, int count, uint64_t key)
   draws[2 * (size_t)m + 1] = rng.uniform();  // the multinomial draw (pf.c:460)
 }
 
+constexpr int kCoarse = 256;
+
+// coarse[j] = cum[(j + 1) * kCoarse]
+__global__ void sample_table(const double *__restrict__ cum, int n_coarse, double *__restrict__ coarse)
+{
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n_coarse) coarse[j] = cum[(size_t)(j + 1) * kCoarse];
+}
+
 struct PickArgs
 {
+  const double *coarse;     // every kCoarse-th table entry, or null
+  int n_coarse;
   const Particle *src;
   int n_src;
   const double *cum;        // n_src + 1 entries
@@ -301,6 +312,21 @@ __global__ void pick_and_copy(const PickArgs a)
   {
     const double r = a.draws[2 * (size_t)m + 1];
     int lo = 0, hi = a.n_src;  // answer = #{ i in 1..n : cum[i] <= r }
+    // Coarse level first: every kCoarse-th table entry lives in a small array
+    // that stays in L1/L2, so only the last ~8 probes touch the big table.
+    if (a.coarse)
+    {
+      int clo = 0, chi = a.n_coarse;   // #{ j in 1..n_coarse : cum[j*kCoarse] <= r }
+      while (clo < chi)
+      {
+        const int mid = clo + ((chi - clo) >> 1);
+        if (__ldg(a.coarse + mid) <= r) clo = mid + 1;
+        else chi = mid;
+      }
+      lo = clo * kCoarse;
+      hi = min(a.n_src, lo + kCoarse - 1);
+      // entries lo+1 .. lo+kCoarse-1 are undecided; cum[lo+kCoarse] > r is known
+    }
     while (lo < hi)
     {
       const int mid = lo + ((hi - lo) >> 1);
@@ -564,6 +590,114 @@ __global__ void cc_link(const BinTable T, unsigned int nslots, int n_valid)
       }
       h = (h + 1) & T.mask;
     }
+  }
+}
+
+// ---- dense grid: tile-local labelling in shared memory, then the tile borders -----
+//
+// A CTA owns a 32 x 8 x 4 brick of the grid (one thread per cell).  The 13
+// forward neighbours that lie inside the brick are united in a shared-memory
+// union-find (tens of cycles per hop instead of an L2 round trip); each cell
+// then points at its brick-local root in the global array.  A second kernel
+// unites across brick faces only -- about a quarter of all edges.
+constexpr int kBrickX = 32, kBrickY = 8, kBrickT = 4;
+constexpr int kBrickCells = kBrickX * kBrickY * kBrickT;
+
+__device__ __forceinline__ unsigned int suf_find(unsigned int *lab, unsigned int x)
+{
+  unsigned int p = lab[x];
+  while (p != x)
+  {
+    const unsigned int gp = lab[p];
+    if (gp != p) lab[x] = gp;
+    x = p;
+    p = gp;
+  }
+  return x;
+}
+
+__device__ __forceinline__ void suf_union(unsigned int *lab, unsigned int a, unsigned int b)
+{
+  for (;;)
+  {
+    a = suf_find(lab, a);
+    b = suf_find(lab, b);
+    if (a == b) return;
+    if (a > b) { unsigned int t = a; a = b; b = t; }
+    if (atomicCAS(&lab[b], b, a) == b) return;
+  }
+}
+
+__global__ void __launch_bounds__(kBrickCells)
+cc_brick_local(const BinTable T, int bricks_x, int bricks_y, int n_valid, unsigned int *cmin)
+{
+  __shared__ unsigned int s_lab[kBrickCells];
+  __shared__ unsigned char s_occ[kBrickCells];
+  const int lx = threadIdx.x & (kBrickX - 1);
+  const int ly = (threadIdx.x / kBrickX) & (kBrickY - 1);
+  const int lt = threadIdx.x / (kBrickX * kBrickY);
+  const int bx = blockIdx.x % bricks_x;
+  const int by = (blockIdx.x / bricks_x) % bricks_y;
+  const int bt = blockIdx.x / (bricks_x * bricks_y);
+  const int ix = bx * kBrickX + lx, iy = by * kBrickY + ly, it = bt * kBrickT + lt;
+  const bool inside = ix < T.ex && iy < T.ey && it < T.et;
+  const unsigned int s = inside ? (unsigned int)((it * T.ey + iy) * T.ex + ix) : 0u;
+  const bool occ = inside && T.first[s] < (unsigned int)n_valid;
+  s_lab[threadIdx.x] = threadIdx.x;
+  s_occ[threadIdx.x] = occ ? 1 : 0;
+  __syncthreads();
+  if (occ)
+  {
+    for (int q = 14; q < 27; q++)
+    {
+      const int dt = q / 9 - 1, dy = (q % 9) / 3 - 1, dx = (q % 9) % 3 - 1;
+      const int nx = lx + dx, ny = ly + dy, nt = lt + dt;
+      if ((unsigned)nx >= (unsigned)kBrickX || (unsigned)ny >= (unsigned)kBrickY ||
+          (unsigned)nt >= (unsigned)kBrickT)
+        continue;
+      const unsigned int nb = (unsigned int)((nt * kBrickY + ny) * kBrickX + nx);
+      if (s_occ[nb]) suf_union(s_lab, threadIdx.x, nb);
+    }
+  }
+  __syncthreads();
+  if (occ)
+  {
+    const unsigned int r = suf_find(s_lab, threadIdx.x);
+    const int rx = r & (kBrickX - 1), ry = (r / kBrickX) & (kBrickY - 1), rt = r / (kBrickX * kBrickY);
+    T.aux[s] = (unsigned int)(((bt * kBrickT + rt) * T.ey + (by * kBrickY + ry)) * T.ex +
+                              (bx * kBrickX + rx));
+    cmin[s] = 0xFFFFFFFFu;
+  }
+}
+
+__global__ void __launch_bounds__(kBrickCells)
+cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid)
+{
+  const int lx = threadIdx.x & (kBrickX - 1);
+  const int ly = (threadIdx.x / kBrickX) & (kBrickY - 1);
+  const int lt = threadIdx.x / (kBrickX * kBrickY);
+  const int bx = blockIdx.x % bricks_x;
+  const int by = (blockIdx.x / bricks_x) % bricks_y;
+  const int bt = blockIdx.x / (bricks_x * bricks_y);
+  const int ix = bx * kBrickX + lx, iy = by * kBrickY + ly, it = bt * kBrickT + lt;
+  if (ix >= T.ex || iy >= T.ey || it >= T.et) return;
+  // only cells on a forward face (or next to the low-x / low-y face, whose
+  // forward neighbours with dx or dy = -1 leave the brick) have work to do
+  if (lx != 0 && lx != kBrickX - 1 && ly != 0 && ly != kBrickY - 1 && lt != kBrickT - 1) return;
+  const unsigned int s = (unsigned int)((it * T.ey + iy) * T.ex + ix);
+  if (T.first[s] >= (unsigned int)n_valid) return;
+  for (int q = 14; q < 27; q++)
+  {
+    const int dt = q / 9 - 1, dy = (q % 9) / 3 - 1, dx = (q % 9) % 3 - 1;
+    const int mx = lx + dx, my = ly + dy, mt = lt + dt;
+    if ((unsigned)mx < (unsigned)kBrickX && (unsigned)my < (unsigned)kBrickY &&
+        (unsigned)mt < (unsigned)kBrickT)
+      continue;                                   // inside the brick: done locally
+    const int nx = ix + dx, ny = iy + dy, nt = it + dt;
+    if ((unsigned)nx >= (unsigned)T.ex || (unsigned)ny >= (unsigned)T.ey || (unsigned)nt >= (unsigned)T.et)
+      continue;
+    const unsigned int nb = (unsigned int)((nt * T.ey + ny) * T.ex + nx);
+    if (T.first[nb] < (unsigned int)n_valid) uf_union(T.aux, s, nb);
   }
 }
 
@@ -960,10 +1094,23 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
   const unsigned int nslots =
       T.dense ? (unsigned int)T.ex * (unsigned int)T.ey * (unsigned int)T.et : c->hash_cap;
   const int sb = (int)((nslots + 255u) / 256u);
-  cc_init<<<sb, 256, 0, st>>>(T, nslots, n, cmin);
-  AMCL_LAUNCH_CHECK();
-  cc_link<<<sb, 256, 0, st>>>(T, nslots, n);
-  AMCL_LAUNCH_CHECK();
+  if (T.dense)
+  {
+    const int bxn = (T.ex + kBrickX - 1) / kBrickX, byn = (T.ey + kBrickY - 1) / kBrickY,
+              btn = (T.et + kBrickT - 1) / kBrickT;
+    const int bricks = bxn * byn * btn;
+    cc_brick_local<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, cmin);
+    AMCL_LAUNCH_CHECK();
+    cc_brick_borders<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n);
+    AMCL_LAUNCH_CHECK();
+  }
+  else
+  {
+    cc_init<<<sb, 256, 0, st>>>(T, nslots, n, cmin);
+    AMCL_LAUNCH_CHECK();
+    cc_link<<<sb, 256, 0, st>>>(T, nslots, n);
+    AMCL_LAUNCH_CHECK();
+  }
   // flatten: rounds of pointer jumping in groups of four, until a round moves nothing
   for (int group = 0; group < 16; group++)
   {
@@ -1176,6 +1323,8 @@ void run_resample(PfCtx *c)
   //    kernel read the chosen poses from their owners' memory over NVLink
   //    (2 x 32 B per output sample instead of shipping the whole set);
   //  * otherwise: all-gather the whole source set in place.
+  Trace tr;
+  tr.mark("start");
   const bool selective_copy =
       pf->selective_resampling != 0 && set_a->n_effective > 0.5 * (set_a->sample_count);
   const bool p2p = sh.on() && c->peers_ready && !c->replicated[ia] && !selective_copy;
@@ -1208,6 +1357,7 @@ void run_resample(PfCtx *c)
   else
     exact_cumsum(c, c->d_set[ia], n_a, c->d_cum);
 
+  tr.mark("table");
   // pf.c:411-413
   double w_diff = 1.0 - pf->w_fast / pf->w_slow;
   if (w_diff < 0.0) w_diff = 0.0;
@@ -1289,6 +1439,16 @@ void run_resample(PfCtx *c)
   pa.peer_chunk = sh.chunk(n_a) > 0 ? sh.chunk(n_a) : 1;
   pa.n_src = n_a;
   pa.cum = c->d_cum;
+  pa.coarse = nullptr;
+  pa.n_coarse = n_a / kCoarse;
+  if (pa.n_coarse >= 64)
+  {
+    // the draws array has room behind the 2*maxs uniforms? no: use the partial-sum scratch
+    ensure_partials(c, pa.n_coarse);
+    sample_table<<<blocks_for(pa.n_coarse, 256), 256, 0, st>>>(c->d_cum, pa.n_coarse, c->d_partials);
+    AMCL_LAUNCH_CHECK();
+    pa.coarse = c->d_partials;
+  }
   pa.draws = c->d_draws;
   pa.injected = d_injected;
   pa.inject_slot = d_inject_slot;
@@ -1308,8 +1468,10 @@ void run_resample(PfCtx *c)
   if (sh.on())
     sh.allgather(c->d_keys, (unsigned long long)sh.chunk(maxs) * sizeof(unsigned long long), sh.user);
 
+  tr.mark("pick+keys");
   // ---- histogram, k_m, KLD cut ---------------------------------------------
   build_histogram(c, maxs);
+  tr.mark("histogram");
   scan_u32(c, c->d_flag, c->d_scan, maxs, I_DISTINCT);
   c->h_ints[I_CUT] = maxs;
   AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_CUT, c->h_ints + I_CUT, sizeof(int),
@@ -1326,6 +1488,7 @@ void run_resample(PfCtx *c)
   AMCL_CUDA(cudaStreamSynchronize(st));
   set_b->sample_count = n;
   set_b->kdtree->leaf_count = (int)k_at_cut;
+  tr.mark("scan+cut");
 
   if (host_stream)
   {
@@ -1370,10 +1533,14 @@ void run_resample(PfCtx *c)
     cudaFree(d_inject_slot);
   }
 
+  tr.mark("weights");
   // pf.c:501-506
   cluster_and_stats(c, ib, n);
+  tr.mark("clusters");
   pf->current_set = ib;
   run_update_converged(c, ib);
+  tr.mark("converged");
+  tr.report("pf_update_resample");
 }
 
 }  // namespace amclb200
