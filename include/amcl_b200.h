@@ -113,6 +113,9 @@ int amclb200_pf_cumulative_table(pf_t *pf, double *out, int capacity);
 /* Device milliseconds (CUDA events) of the last action / sensor / resample call. */
 void amclb200_pf_last_timings(pf_t *pf, float out_ms[3]);
 
+/* Device milliseconds the distance-transform kernels of the last map_update_cspace took. */
+double amclb200_map_last_edt_ms(map_t *map);
+
 /* Batched map_calc_range on the device: n rays (ox, oy, oa) -> ranges. */
 void amclb200_map_calc_ranges(map_t *map, const double *rays_xya, int n, double max_range,
                               double *out_ranges);

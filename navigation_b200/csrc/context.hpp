@@ -66,7 +66,10 @@ struct MapCtx
   uint16_t *d_code = nullptr;     // tiled distance codes
   uint64_t *d_blocked = nullptr;  // 8x8-cell bit tiles: bit set = ray stops here
   int btiles_x = 0, btiles_y = 0;
-  uint8_t *d_rowdist = nullptr;   // EDT pass-1 scratch (uint16 when R > 254)
+  uint8_t *d_rowdist = nullptr;   // EDT scratch: distance along the row, one byte per cell
+  unsigned long long *d_rowbits = nullptr;  // EDT scratch: occupancy bit strings per row
+  size_t rowbits_cap = 0;
+  float ms_edt = 0;               // device time of the last distance transform (3 kernels)
   std::vector<double> dist_of_code;  // host: code -> metres (incl. sentinel)
 
   int code_far() const { return R * R + 1; }

@@ -168,7 +168,6 @@ __global__ void cs_classify(const double *__restrict__ tile_sum, const double *_
                             int tiles, int n, int *__restrict__ tile_class, int *dirty_count)
 {
   __shared__ double s_part[1024];
-  __shared__ double s_total;
   // pass 1: grand total (each thread a contiguous slab, then a serial combine)
   const int per = (tiles + blockDim.x - 1) / blockDim.x;
   const int lo = threadIdx.x * per, hi = min(tiles, lo + per);
@@ -185,7 +184,6 @@ __global__ void cs_classify(const double *__restrict__ tile_sum, const double *_
       s_part[k] = run;            // exclusive prefix of the slabs
       run += v;
     }
-    s_total = run;
   }
   __syncthreads();
   // Weights are non-negative, so every partial sum -- the sequential one and this

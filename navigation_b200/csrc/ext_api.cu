@@ -86,6 +86,13 @@ void amclb200_pf_last_timings(pf_t *pf, float out_ms[3])
   out_ms[2] = c->ms_resample;
 }
 
+// Device milliseconds of the distance-transform kernels of the last map_update_cspace.
+double amclb200_map_last_edt_ms(map_t *map)
+{
+  MapCtx *m = map_ctx(map, false);
+  return m ? (double)m->ms_edt : -1.0;
+}
+
 void amclb200_map_calc_ranges(map_t *map, const double *rays_xya, int n, double max_range,
                               double *out_ranges)
 {

@@ -15,7 +15,9 @@
 #include <math.h>
 #include <string.h>
 
+#include <functional>
 #include <mutex>
+#include <thread>
 #include <unordered_map>
 
 #include "context.hpp"
@@ -142,7 +144,7 @@ MapCtx *map_ctx(map_t *map, bool create)
   AMCL_CUDA(cudaMalloc(&m->d_occ, cells));
   AMCL_CUDA(cudaMalloc(&m->d_code, (size_t)m->tiles_x * m->tiles_y * 16 * sizeof(uint16_t)));
   AMCL_CUDA(cudaMalloc(&m->d_blocked, (size_t)m->btiles_x * m->btiles_y * sizeof(uint64_t)));
-  AMCL_CUDA(cudaMalloc(&m->d_rowdist, cells * sizeof(uint16_t)));
+  AMCL_CUDA(cudaMalloc(&m->d_rowdist, cells));
   r[map] = m;
   return m;
 }
@@ -157,6 +159,7 @@ void map_ctx_release(map_t *map)
   cudaFree(m->d_code);
   cudaFree(m->d_blocked);
   cudaFree(m->d_rowdist);
+  if (m->d_rowbits) cudaFree(m->d_rowbits);
   delete m;
   r.erase(it);
 }
@@ -187,114 +190,188 @@ __global__ void build_blocked_bits(const int8_t *__restrict__ occ, int sx, int s
   bits[t] = word;
 }
 
-// EDT pass 1: for every cell the distance (in cells, along the row) to the
-// nearest occupied cell of the same row, capped at R+1.  One block handles a
-// row segment; the segment plus an R-cell apron sits in shared memory.
-constexpr int kRowSeg = 512;
+// ---- exact bounded EDT, three kernels --------------------------------------------
+//
+// (1) edt_pack_rows: occupancy (== +1) of every row as a bit string, 64 cells per
+//     word, zero words of padding on both sides of each row.
+// (2) edt_row_bits:  g(i, j) = distance along row j from cell i to the nearest
+//     occupied cell, capped at R+1, read off the bit string with count-leading /
+//     trailing-zero instructions (no neighbour scan).  One byte per cell.
+// (3) edt_col_pass:  d2(i, j) = min over |dj| <= R of dj^2 + g(i, j+dj)^2,
+//     thresholded at R^2; each thread resolves four neighbouring cells from
+//     packed bytes; results leave through shared memory so that every 4x4 tile
+//     of codes is one contiguous 32-byte sector.
 
-__global__ void edt_row_pass(const int8_t *__restrict__ occ, int sx, int sy, int R,
-                             uint16_t *__restrict__ rowdist)
+__global__ void edt_pack_rows(const int8_t *__restrict__ occ, int sx, int sy, int words, int pad,
+                              unsigned long long *__restrict__ bits)
 {
-  extern __shared__ unsigned char s_occ[];  // kRowSeg + 2R
-  const int j = blockIdx.y;
-  const int i0 = blockIdx.x * kRowSeg;
-  const int span = kRowSeg + 2 * R;
-  const int8_t *row = occ + (size_t)j * sx;
-  for (int k = threadIdx.x; k < span; k += blockDim.x)
+  const int lane = threadIdx.x & 31;
+  const long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int stride = words + 2 * pad;
+  const int j = (int)(warp / stride), w = (int)(warp % stride) - pad;
+  if (j >= sy) return;
+  unsigned long long word = 0ull;
+  if (w >= 0 && w < words)
   {
-    int i = i0 - R + k;
-    s_occ[k] = (i >= 0 && i < sx && row[i] == 1) ? 1 : 0;
+    const int8_t *row = occ + (size_t)j * sx;
+    const int i0 = w * 64 + lane, i1 = i0 + 32;
+    const unsigned lo = __ballot_sync(kFullMask, i0 < sx && row[i0] == 1);
+    const unsigned hi = __ballot_sync(kFullMask, i1 < sx && row[i1] == 1);
+    word = (unsigned long long)lo | ((unsigned long long)hi << 32);
   }
-  __syncthreads();
-  for (int k = threadIdx.x; k < kRowSeg; k += blockDim.x)
-  {
-    int i = i0 + k;
-    if (i >= sx) break;
-    int c = k + R;
-    int best = R + 1;
-    for (int d = 0; d <= R; d++)
-    {
-      if (s_occ[c - d] | s_occ[c + d])
-      {
-        best = d;
-        break;
-      }
-    }
-    rowdist[(size_t)j * sx + i] = (uint16_t)best;
-  }
+  if (lane == 0) bits[(size_t)j * stride + (w + pad)] = word;
 }
 
-// EDT pass 2: d2(i,j) = min over |dj| <= R of dj^2 + g(i, j+dj)^2, thresholded
-// at R^2.  A block owns a 32 (x) by 32 (y) cell patch; the column window
-// (32 + 2R rows) of g is staged in shared memory; results leave through shared
-// memory so that each 4x4 tile is written as one contiguous 32-byte sector.
-constexpr int kPatch = 32;
-
-__global__ void edt_col_pass(const uint16_t *__restrict__ rowdist, int sx, int sy, int R,
-                             int tiles_x, uint16_t *__restrict__ code)
+__global__ void edt_row_bits(const unsigned long long *__restrict__ bits, int sx, int sy, int words,
+                             int pad, int R, unsigned char *__restrict__ g)
 {
-  extern __shared__ uint16_t s_g[];  // (kPatch + 2R) * kPatch, then kPatch*kPatch out
-  const int i0 = blockIdx.x * kPatch, j0 = blockIdx.y * kPatch;
-  const int rows = kPatch + 2 * R;
-  const int far = R + 1;
-  for (int k = threadIdx.x; k < rows * kPatch; k += blockDim.x)
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y;
+  if (i >= sx) return;
+  const int stride = words + 2 * pad;
+  const unsigned long long *A = bits + (size_t)j * stride + pad;   // A[-pad .. words+pad)
+  const int k = i >> 6, sft = i & 63;
+  // towards lower x: bits i, i-1, ... ; towards higher x: bits i, i+1, ...
+  int left = R + 1, right = R + 1;
   {
-    int lj = k / kPatch, li = k % kPatch;
-    int j = j0 - R + lj, i = i0 + li;
-    uint16_t g = (uint16_t)far;
-    if (j >= 0 && j < sy && i < sx) g = rowdist[(size_t)j * sx + i];
-    s_g[k] = g;
+    unsigned long long w = A[k] << (63 - sft);          // bit i at the top
+    int base = 0;
+    int kk = k;
+    int have = sft + 1;                                  // valid bits in w
+    for (;;)
+    {
+      if (w) { left = base + __clzll((long long)w); break; }
+      base += have;
+      if (base > R) break;
+      kk--;
+      w = A[kk];
+      have = 64;
+    }
+  }
+  {
+    unsigned long long w = A[k] >> sft;                  // bit i at the bottom
+    int base = 0;
+    int kk = k;
+    int have = 64 - sft;
+    for (;;)
+    {
+      if (w) { right = base + __ffsll((long long)w) - 1; break; }
+      base += have;
+      if (base > R) break;
+      kk++;
+      w = A[kk];
+      have = 64;
+    }
+  }
+  int best = left < right ? left : right;
+  if (best > R + 1) best = R + 1;
+  g[(size_t)j * sx + i] = (unsigned char)best;
+}
+
+constexpr int kPatchX = 64, kPatchY = 32;
+
+__global__ void __launch_bounds__(256)
+edt_col_pass(const unsigned char *__restrict__ g, int sx, int sy, int R, int tiles_x,
+             uint16_t *__restrict__ code)
+{
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  unsigned char *s_g = s_raw;                                        // (kPatchY + 2R) x kPatchX
+  const int rows = kPatchY + 2 * R;
+  uint16_t *s_out = reinterpret_cast<uint16_t *>(s_raw + (((size_t)rows * kPatchX + 15) & ~(size_t)15));
+  const int i0 = blockIdx.x * kPatchX, j0 = blockIdx.y * kPatchY;
+  const unsigned char far = (unsigned char)(R + 1);
+  for (int k = threadIdx.x; k < rows * kPatchX; k += blockDim.x)
+  {
+    const int lj = k / kPatchX, li = k % kPatchX;
+    const int j = j0 - R + lj, i = i0 + li;
+    s_g[k] = (j >= 0 && j < sy && i < sx) ? g[(size_t)j * sx + i] : far;
   }
   __syncthreads();
-  uint16_t *s_out = s_g + rows * kPatch;
   const int R2 = R * R;
-  for (int k = threadIdx.x; k < kPatch * kPatch; k += blockDim.x)
+  for (int quad = threadIdx.x; quad < kPatchX * kPatchY / 4; quad += blockDim.x)
   {
-    int lj = k / kPatch, li = k % kPatch;
-    int best = R2 + 1;
-    // walk outwards from the own row; stop once dj^2 alone cannot improve
+    const int lj = quad / (kPatchX / 4), li = (quad % (kPatchX / 4)) * 4;
+    int best[4] = {R2 + 1, R2 + 1, R2 + 1, R2 + 1};
     for (int d = 0; d <= R; d++)
     {
-      int dd = d * d;
-      if (dd >= best) break;
-      int ga = s_g[(lj + R - d) * kPatch + li];
-      int gb = s_g[(lj + R + d) * kPatch + li];
-      int g = ga < gb ? ga : gb;
-      int v = dd + g * g;
-      if (v < best) best = v;
+      const int dd = d * d;
+      const int worst = max(max(best[0], best[1]), max(best[2], best[3]));
+      if (dd >= worst) break;                       // farther rows cannot improve any of the four
+      const unsigned ga = *reinterpret_cast<const unsigned *>(s_g + (lj + R - d) * kPatchX + li);
+      const unsigned gb = *reinterpret_cast<const unsigned *>(s_g + (lj + R + d) * kPatchX + li);
+      const unsigned m = __vminu4(ga, gb);
+#pragma unroll
+      for (int b = 0; b < 4; b++)
+      {
+        const int gg = (int)((m >> (8 * b)) & 255u);
+        const int v = dd + gg * gg;
+        best[b] = v < best[b] ? v : best[b];
+      }
     }
-    if (best > R2) best = R2 + 1;
-    // position inside the patch's 8x8 grid of 4x4 tiles
-    int tj = lj >> 2, ti = li >> 2;
-    s_out[(tj * (kPatch / kTile) + ti) * 16 + (lj & 3) * 4 + (li & 3)] = (uint16_t)best;
+    const int tj = lj >> 2, ti = li >> 2;           // the quad is one row of one 4x4 tile
+    uint16_t *o = s_out + (tj * (kPatchX / kTile) + ti) * 16 + (lj & 3) * 4;
+#pragma unroll
+    for (int b = 0; b < 4; b++) o[b] = (uint16_t)(best[b] > R2 ? R2 + 1 : best[b]);
   }
   __syncthreads();
-  // 64 tiles per patch, 16 codes (32 B) each; a thread moves one 8-byte quarter
-  const int quarters = (kPatch / kTile) * (kPatch / kTile) * 4;
-  for (int q = threadIdx.x; q < quarters; q += blockDim.x)
+  // (kPatchX/4) x (kPatchY/4) tiles of 32 bytes; a thread moves one 16-byte half
+  const int halves = (kPatchX / kTile) * (kPatchY / kTile) * 2;
+  for (int q = threadIdx.x; q < halves; q += blockDim.x)
   {
-    int tile = q >> 2, part = q & 3;
-    int tj = tile / (kPatch / kTile), ti = tile % (kPatch / kTile);
-    int gi = (i0 >> 2) + ti, gj = (j0 >> 2) + tj;
+    const int tile = q >> 1, part = q & 1;
+    const int tj = tile / (kPatchX / kTile), ti = tile % (kPatchX / kTile);
+    const int gi = (i0 >> 2) + ti, gj = (j0 >> 2) + tj;
     if (gi * kTile >= sx || gj * kTile >= sy) continue;
-    const uint2 *src = reinterpret_cast<const uint2 *>(s_out + tile * 16 + part * 4);
-    uint2 *dst = reinterpret_cast<uint2 *>(code + ((size_t)gj * tiles_x + gi) * 16 + part * 4);
+    const uint4 *src = reinterpret_cast<const uint4 *>(s_out + tile * 16 + part * 8);
+    uint4 *dst = reinterpret_cast<uint4 *>(code + ((size_t)gj * tiles_x + gi) * 16 + part * 8);
     *dst = *src;
   }
 }
 
 // ------------------------------------------------------------ host-side glue --
 
+// The caller's grid is an array of 16-byte structs; converting 16 M of them to
+// and from the packed device formats is host-memory bound, so the row loops are
+// spread over the host cores.
+static void parallel_rows(int rows, const std::function<void(int, int)> &body)
+{
+  unsigned hw = std::thread::hardware_concurrency();
+  int nt = (int)(hw ? (hw > 16 ? 16 : hw) : 4);
+  if (rows < 256 || nt < 2)
+  {
+    body(0, rows);
+    return;
+  }
+  std::vector<std::thread> pool;
+  const int per = (rows + nt - 1) / nt;
+  for (int t = 0; t < nt; t++)
+  {
+    const int lo = t * per, hi = lo + per < rows ? lo + per : rows;
+    if (lo >= hi) break;
+    pool.emplace_back(body, lo, hi);
+  }
+  for (auto &th : pool) th.join();
+}
+
+
 void map_upload_occupancy(MapCtx *m)
 {
   const map_t *map = m->host;
   size_t cells = (size_t)m->sx * m->sy;
   std::vector<int8_t> occ(cells);
-  for (size_t k = 0; k < cells; k++)
-  {
-    int s = map->cells[k].occ_state;
-    occ[k] = (int8_t)(s > 0 ? 1 : (s < 0 ? -1 : 0));
-  }
+  const int sx = m->sx;
+  parallel_rows(m->sy, [&](int j0, int j1) {
+    for (int j = j0; j < j1; j++)
+    {
+      const map_cell_t *row = map->cells + (size_t)j * sx;
+      int8_t *o = occ.data() + (size_t)j * sx;
+      for (int i = 0; i < sx; i++)
+      {
+        const int st = row[i].occ_state;
+        o[i] = (int8_t)(st > 0 ? 1 : (st < 0 ? -1 : 0));
+      }
+    }
+  });
   cudaStream_t st = globals().stream;
   AMCL_CUDA(cudaMemcpyAsync(m->d_occ, occ.data(), cells, cudaMemcpyHostToDevice, st));
   int nt = m->btiles_x * m->btiles_y;
@@ -326,18 +403,42 @@ void map_build_distance_codes(MapCtx *m, double max_occ_dist)
   set_code_table(m, max_occ_dist);
   cudaStream_t st = globals().stream;
   const int R = m->R;
-  dim3 g1((m->sx + kRowSeg - 1) / kRowSeg, m->sy);
-  edt_row_pass<<<g1, 256, kRowSeg + 2 * R, st>>>(m->d_occ, m->sx, m->sy, R,
-                                                 (uint16_t *)m->d_rowdist);
+  cudaEvent_t ev0, ev1;
+  AMCL_CUDA(cudaEventCreate(&ev0));
+  AMCL_CUDA(cudaEventCreate(&ev1));
+  AMCL_CUDA(cudaEventRecord(ev0, st));
+  const int words = (m->sx + 63) / 64;
+  const int pad = (R + 1 + 63) / 64 + 1;
+  const size_t nbits = (size_t)m->sy * (words + 2 * pad);
+  if (nbits > m->rowbits_cap)
+  {
+    if (m->d_rowbits) cudaFree(m->d_rowbits);
+    m->rowbits_cap = nbits;
+    AMCL_CUDA(cudaMalloc(&m->d_rowbits, nbits * sizeof(unsigned long long)));
+  }
+  {
+    const long long warps = (long long)m->sy * (words + 2 * pad);
+    edt_pack_rows<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(m->d_occ, m->sx, m->sy, words, pad,
+                                                               m->d_rowbits);
+    AMCL_LAUNCH_CHECK();
+  }
+  if (m->sy > 65535) AMCL_FATAL("maps taller than 65535 rows are not supported (%d)", m->sy);
+  dim3 g1((m->sx + 255) / 256, m->sy);
+  edt_row_bits<<<g1, 256, 0, st>>>(m->d_rowbits, m->sx, m->sy, words, pad, R, m->d_rowdist);
   AMCL_LAUNCH_CHECK();
-  dim3 g2((m->sx + kPatch - 1) / kPatch, (m->sy + kPatch - 1) / kPatch);
-  size_t smem = ((size_t)(kPatch + 2 * R) * kPatch + kPatch * kPatch) * sizeof(uint16_t);
+  dim3 g2((m->sx + kPatchX - 1) / kPatchX, (m->sy + kPatchY - 1) / kPatchY);
+  size_t smem = (((size_t)(kPatchY + 2 * R) * kPatchX + 15) & ~(size_t)15) +
+                (size_t)kPatchX * kPatchY * sizeof(uint16_t);
   if (smem > 48 * 1024)
     AMCL_CUDA(cudaFuncSetAttribute(edt_col_pass, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)smem));
-  edt_col_pass<<<g2, 256, smem, st>>>((const uint16_t *)m->d_rowdist, m->sx, m->sy, R,
-                                      m->tiles_x, m->d_code);
+  edt_col_pass<<<g2, 256, smem, st>>>(m->d_rowdist, m->sx, m->sy, R, m->tiles_x, m->d_code);
   AMCL_LAUNCH_CHECK();
+  AMCL_CUDA(cudaEventRecord(ev1, st));
+  AMCL_CUDA(cudaEventSynchronize(ev1));
+  AMCL_CUDA(cudaEventElapsedTime(&m->ms_edt, ev0, ev1));
+  cudaEventDestroy(ev0);
+  cudaEventDestroy(ev1);
   m->dist_valid = true;
   m->generation++;
 }
@@ -351,13 +452,15 @@ void map_codes_to_host_cells(MapCtx *m)
   AMCL_CUDA(cudaStreamSynchronize(globals().stream));
   map_t *map = m->host;
   const double *lut = m->dist_of_code.data();
-  for (int j = 0; j < m->sy; j++)
-  {
-    const uint16_t *trow = codes.data() + (size_t)(j >> 2) * m->tiles_x * 16 + (j & 3) * 4;
-    map_cell_t *crow = map->cells + (size_t)j * m->sx;
-    for (int i = 0; i < m->sx; i++)
-      crow[i].occ_dist = lut[trow[(size_t)(i >> 2) * 16 + (i & 3)]];
-  }
+  parallel_rows(m->sy, [&](int j0, int j1) {
+    for (int j = j0; j < j1; j++)
+    {
+      const uint16_t *trow = codes.data() + (size_t)(j >> 2) * m->tiles_x * 16 + (j & 3) * 4;
+      map_cell_t *crow = map->cells + (size_t)j * m->sx;
+      for (int i = 0; i < m->sx; i++)
+        crow[i].occ_dist = lut[trow[(size_t)(i >> 2) * 16 + (i & 3)]];
+    }
+  });
   map->max_occ_dist = m->max_occ_dist;
 }
 

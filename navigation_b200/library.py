@@ -30,6 +30,7 @@ EXTENSION_SYMBOLS = {
     "amclb200_pf_cluster_labels": (C.c_int, [abi.pf_p, C.c_void_p, C.c_int]),
     "amclb200_pf_cumulative_table": (C.c_int, [abi.pf_p, C.c_void_p, C.c_int]),
     "amclb200_pf_last_timings": (None, [abi.pf_p, C.POINTER(C.c_float)]),
+    "amclb200_map_last_edt_ms": (C.c_double, [abi.map_p]),
     "amclb200_map_calc_ranges": (None, [abi.map_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p]),
     "amclb200_pf_load_device": (None, [abi.pf_p, C.c_void_p, C.c_int]),
     "amclb200_pf_set_shard": (None, [abi.pf_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
