@@ -552,3 +552,66 @@ def test_k4_full_size_resample_properties(lib, port):
     assert sum(side.cur.clusters[c].count for c in range(len(tab))) == cnt
     lib.amclb200_set_rng(library.RNG_DRAND48, 0)
     side.close()
+
+
+# ------------------------------------------ init_model and recovery injection ----
+
+def test_pf_init_model_matches_reference(lib, ref):
+    """pf_init_model (pf.c:178-211) with the node's uniform free-space generator:
+    host callbacks on the shared drand48 stream, so poses are bit-identical."""
+    occ = synth.rooms_map(300, seed=6)
+    out = []
+    for L in (ref, lib):
+        side = Side(L, occ)
+        side.alloc(50, 4000)
+        side.seed(17)
+        side.init_uniform()
+        out.append((side.samples(), side.cur.cluster_count, side.cur.kdtree.contents.leaf_count,
+                    np.array(side.cur.mean.tolist())))
+        side.close()
+    (sa, ca, ka, ma), (sb, cb, kb, mb) = out
+    assert np.array_equal(sa, sb)
+    assert ca == cb and ka == kb
+    assert np.allclose(ma, mb, rtol=1e-9, atol=1e-12)
+
+
+def test_recovery_injection_matches_reference(lib, ref):
+    """w_diff > 0 (pf.c:411-431,487-489): some output samples are fresh poses from
+    the caller's generator, drawn from the same drand48 stream in the same
+    order; afterwards both streams must stand at the same place."""
+    occ = synth.rooms_map(300, seed=6)
+    pose = synth.room_centre_pose(300, 0.05)
+    n = 3000
+    cloud = synth.gaussian_cloud(pose, (0.3, 0.3, 0.1), n, 2)
+    w = np.random.default_rng(4).gamma(0.8, size=n)
+    cloud[:, 3] = w / w.sum()
+    res = []
+    for L in (ref, lib):
+        side = Side(L, occ)
+        side.alloc(100, n, alpha_slow=0.001, alpha_fast=0.1)
+        side.set_samples(cloud)
+        side.pf.contents.w_slow = 1.0e-3      # w_fast / w_slow = 0.6 -> w_diff = 0.4
+        side.pf.contents.w_fast = 0.6e-3
+        side.seed(23)
+        side.resample()
+        s = side.samples()
+        # next uniform of the shared stream: equal iff both consumed the same number
+        if L is ref:
+            nxt = L.drand48()
+        else:
+            libc = C.CDLL(None)
+            libc.drand48.restype = C.c_double
+            nxt = libc.drand48()
+        res.append((s, side.cur.kdtree.contents.leaf_count, side.cur.cluster_count,
+                    side.pf.contents.w_slow, side.pf.contents.w_fast, nxt))
+        side.close()
+    (sa, ka, ca, wsa, wfa, na), (sb, kb, cb, wsb, wfb, nb) = res
+    assert sa.shape == sb.shape
+    assert np.array_equal(sa, sb)
+    assert ka == kb and ca == cb
+    assert wsa == wsb == 0.0 and wfa == wfb == 0.0     # averages reset after injecting
+    assert na == nb
+    # a sizeable share of the new set really is injected (not copies of old poses)
+    old = {tuple(r) for r in cloud[:, :3]}
+    injected = sum(tuple(r) not in old for r in sb[:, :3])
+    assert 0.3 * len(sb) < injected < 0.5 * len(sb)
