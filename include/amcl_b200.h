@@ -79,6 +79,13 @@ void amclb200_set_stream(void *cuda_stream);
  * reference's exact order (parity with the reference for a given srand48). */
 void amclb200_set_rng(int mode, uint64_t seed);
 
+/* on = 1 (default): pf_alloc seeds drand48 from the clock and pf_init re-seeds it
+ * from a per-process counter, exactly as the reference does (pf.c:55, pf_pdf.c:68).
+ * on = 0: the library never seeds; a caller that seeds the stream itself gets
+ * reproducible runs. */
+void amclb200_set_reseed(int on);
+int amclb200_get_reseed(void);
+
 /* Host mirror policy for pf_sample_set_t::samples.  eager = 1 (default): every
  * pf_update_* / UpdateAction / UpdateSensor call ends with a device-to-host
  * copy of the current set, so callers that read samples[] directly

@@ -332,6 +332,13 @@ void eigen_decomposition(double A[3][3], double V[3][3], double d[3])
 // ----------------------------------------------------------- pf_pdf.c:40-147 --
 
 static unsigned int g_pdf_seed = 0;   // pf_pdf.c:38
+static int g_reseed = 1;
+
+// amclb200_set_reseed(0): the library stops re-seeding the process-wide drand48
+// stream (pf_alloc's srand48(time), pf_pdf_gaussian_alloc's srand48(++counter)),
+// so a caller that seeds the stream itself gets reproducible runs.
+void amclb200_set_reseed(int on) { g_reseed = on != 0; }
+int amclb200_get_reseed(void) { return g_reseed; }
 
 pf_pdf_gaussian_t *pf_pdf_gaussian_alloc(pf_vector_t x, pf_matrix_t cx)
 {
@@ -345,7 +352,8 @@ pf_pdf_gaussian_t *pf_pdf_gaussian_alloc(pf_vector_t x, pf_matrix_t cx)
   pdf->cd.v[2] = sqrt(cd.m[2][2]);
   // The reference re-seeds the global stream with a per-process counter here
   // (pf_pdf.c:68), which makes pf_init deterministic; kept for that reason.
-  srand48(++g_pdf_seed);
+  ++g_pdf_seed;
+  if (g_reseed) srand48(g_pdf_seed);
   return pdf;
 }
 

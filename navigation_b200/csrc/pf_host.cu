@@ -17,6 +17,8 @@
 #include "amcl/pf/pf_pdf.h"
 #include "context.hpp"
 
+extern "C" int amclb200_get_reseed(void);   // host_math.cpp
+
 namespace amcl
 {
 bool amclb200_is_device_laser_model(pf_sensor_model_fn_t fn);  // sensor_dev.cu
@@ -222,7 +224,7 @@ pf_t *pf_alloc(int min_samples, int max_samples, double alpha_slow, double alpha
   if (max_samples < 1) AMCL_FATAL("pf_alloc: max_samples = %d", max_samples);
   // The reference seeds the process-wide drand48 stream here (pf.c:55); the
   // caller's own pose generator draws from that stream too, so keep doing it.
-  srand48(time(NULL));
+  if (amclb200_get_reseed()) srand48(time(NULL));
 
   pf_t *pf = (pf_t *)calloc(1, sizeof(pf_t));
   pf->random_pose_fn = random_pose_fn;

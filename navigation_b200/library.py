@@ -21,6 +21,8 @@ EXTENSION_SYMBOLS = {
     "amclb200_version": (C.c_char_p, []),
     "amclb200_set_stream": (None, [C.c_void_p]),
     "amclb200_set_rng": (None, [C.c_int, C.c_uint64]),
+    "amclb200_set_reseed": (None, [C.c_int]),
+    "amclb200_get_reseed": (C.c_int, []),
     "amclb200_set_mirror": (None, [abi.pf_p, C.c_int]),
     "amclb200_pf_pull_samples": (None, [abi.pf_p]),
     "amclb200_pf_push_samples": (None, [abi.pf_p]),
