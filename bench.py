@@ -336,10 +336,19 @@ def b200_arm(args):
     peak = gather_rate * 32.0 / 1e9
     peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
     hbm = json.load(open(peaks_file))["hbm_gbs"] if os.path.exists(peaks_file) else 6650.0
+    traffic = None
+    tfile = os.path.join(ROOT, "profiles", "lf_traffic.json")
+    if os.path.exists(tfile) and args.beams == N_BEAMS and args.map_size == MAP_SIZE:
+        traffic = json.load(open(tfile)).get(str(n_local))     # measured by ncu for this launch shape
     roofline = {
         "kernel": "likelihood_field_kernel<LF>", "bound": "l2_gather",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": None,
+        "traffic": traffic,
+        "note": ("algorithmic bytes = 32 B per evaluation (one L2 sector per uncorrelated gather) + 40 B per "
+                 "particle (SURVEY.md 8d); the map is L2-resident, so HBM is not the binding bound: DRAM "
+                 "traffic ('traffic', ncu) is ~64 B per particle.  Neighbouring beams share sectors, which "
+                 "is why achieved exceeds the uncorrelated-gather peak; the kernel itself is L1TEX-bound "
+                 "(75 % of peak, ncu)"),
         "evals_per_s": k_evals / (k_ms * 1e-3), "gather_peak_per_s": gather_rate,
         "kernel_ms": k_ms, "share_of_step": k_ms / ms_step,
         "peak_source": "measured live: uncorrelated 2-byte gathers over a %d MB table (one 32-B sector each)" % (map_bytes >> 20),
