@@ -170,8 +170,8 @@ struct PfCtx
   // laser staging (beam table + LUT), sized on demand
   double *d_scan_tab = nullptr;
   int scan_tab_cap = 0;
-  double *d_lut = nullptr;
-  int lut_cap = 0;
+  double *d_skip = nullptr;       // beam-skip pass: per-beam agreement counts + code->agree bytes
+  int skip_cap = 0;
 
   uint64_t step = 0;              // counter feeding the Philox key
   unsigned long long draws_used = 0;
@@ -209,7 +209,7 @@ struct LaserScanHost
 double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
                             const double laser_pose[3], const LaserScanHost &scan,
                             const std::vector<double> &lut, const int *mask_or_null,
-                            int n_beam_slots, int *agree_counts_or_null,
+                            int *agree_counts_or_null,
                             const std::vector<unsigned char> *agree_lut);
 double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3],
                       const LaserScanHost &scan, double range_max, const double zp[6]);

@@ -444,10 +444,9 @@ static int persistent_grid(K kernel, int threads, size_t smem)
 double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
                             const double laser_pose[3], const LaserScanHost &scan,
                             const std::vector<double> &lut, const int *mask_or_null,
-                            int n_beam_slots, int *agree_counts_or_null,
+                            int *agree_counts_or_null,
                             const std::vector<unsigned char> *agree_lut)
 {
-  (void)n_beam_slots;
   cudaStream_t st = globals().stream;
   const int n_all = c->host->sets[which].sample_count;
   const int lo = c->shard.lo(n_all);
@@ -488,14 +487,14 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   if (count_mode)
   {
     size_t bytes = (size_t)ncodes_pad + sizeof(int) * (size_t)(nb + 1);
-    if ((int)bytes > c->lut_cap)
+    if ((int)bytes > c->skip_cap)
     {
-      if (c->d_lut) cudaFree(c->d_lut);
-      c->lut_cap = (int)bytes + 4096;
-      AMCL_CUDA(cudaMalloc(&c->d_lut, (size_t)c->lut_cap));
+      if (c->d_skip) cudaFree(c->d_skip);
+      c->skip_cap = (int)bytes + 4096;
+      AMCL_CUDA(cudaMalloc(&c->d_skip, (size_t)c->skip_cap));
     }
-    d_counts = reinterpret_cast<int *>(c->d_lut);
-    d_agree = reinterpret_cast<unsigned char *>(c->d_lut) + sizeof(int) * (size_t)(nb + 1);
+    d_counts = reinterpret_cast<int *>(c->d_skip);
+    d_agree = reinterpret_cast<unsigned char *>(c->d_skip) + sizeof(int) * (size_t)(nb + 1);
     AMCL_CUDA(cudaMemsetAsync(d_counts, 0, sizeof(int) * (size_t)(nb + 1), st));
     AMCL_CUDA(cudaMemcpyAsync(d_agree, agree_lut->data(), agree_lut->size(),
                               cudaMemcpyHostToDevice, st));
@@ -903,7 +902,7 @@ double AMCLLaser::LikelihoodFieldModel(AMCLLaserData *data, pf_sample_set_t *set
     pz += self->z_rand * z_rand_mult;
     lut[k] = pz * pz * pz;
   }
-  return run_likelihood_field(c, which, m, 1, self->laser_pose.v, scan, lut, nullptr, 0,
+  return run_likelihood_field(c, which, m, 1, self->laser_pose.v, scan, lut, nullptr,
                               nullptr, nullptr);
 }
 
@@ -940,7 +939,7 @@ double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t 
   }
   const bool do_beamskip = self->do_beamskip && set->converged;   // :342-344
   if (!do_beamskip)
-    return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, nullptr, 0,
+    return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, nullptr,
                                 nullptr, nullptr);
 
   // Beam skipping (:446-489) as two device passes instead of the reference's
@@ -951,7 +950,7 @@ double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t 
   std::vector<int> obs_count(slots, 0), obs_mask(slots, 0);
   for (size_t k = 0; k < scan.beam_ind.size(); k++)
     if (scan.beam_ind[k] >= slots) AMCL_FATAL("beam index beyond max_beams");
-  run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, nullptr, slots,
+  run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, nullptr,
                        obs_count.data(), &agree);
   int skipped = 0;
   for (int b = 0; b < slots; b++)
@@ -975,7 +974,7 @@ double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t 
   // either case: the reference would read stale scratch for them when `error`
   // is set (:479-482), which has no defined value.  See DESIGN.md.
   return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, obs_mask.data(),
-                              slots, nullptr, nullptr);
+                              nullptr, nullptr);
 }
 
 // amcl_laser.cpp:144-213
