@@ -345,6 +345,11 @@ __global__ void pick_and_copy(const PickArgs a)
   if (a.write_keys) a.keys[m] = pose_key(s, a.bin_x, a.bin_y, a.bin_t);
 }
 
+__global__ void negate_ints(int *v, int n)
+{
+  if ((int)threadIdx.x < n) v[threadIdx.x] = -v[threadIdx.x];
+}
+
 __global__ void pack_weights(const Particle *__restrict__ set, int n, double *__restrict__ out)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -419,11 +424,13 @@ __global__ void key_bounds(const unsigned long long *__restrict__ keys, int n, i
   }
 }
 
-__global__ void bin_insert(const unsigned long long *__restrict__ keys, int n, const BinTable T,
-                           unsigned int *slot_of)
+// Samples [base, base + n): keys / slot_of are indexed by the GLOBAL sample index.
+__global__ void bin_insert(const unsigned long long *__restrict__ keys, int base, int n,
+                           const BinTable T, unsigned int *slot_of)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= n) return;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int m = base + t;
   const unsigned long long key = keys[m];
   if (T.dense)
   {
@@ -451,11 +458,32 @@ __global__ void bin_insert(const unsigned long long *__restrict__ keys, int n, c
   }
 }
 
-__global__ void mark_first(const unsigned int *__restrict__ first, const unsigned int *__restrict__ slot_of,
-                           int n, unsigned int *flag)
+// Slot of samples [base, base + n) of `set` in an already built table (read-only).
+__global__ void bin_lookup(const Particle *__restrict__ set, int base, int n, const BinTable T,
+                           double bin_x, double bin_y, double bin_t, unsigned int *slot_of)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= n) return;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int m = base + t;
+  const unsigned long long key = pose_key(load_particle(set + m), bin_x, bin_y, bin_t);
+  if (T.dense)
+  {
+    int kx, ky, kt;
+    unpack_key(key, &kx, &ky, &kt);
+    slot_of[m] = (unsigned int)(((kt - T.t0) * T.ey + (ky - T.y0)) * T.ex + (kx - T.x0));
+    return;
+  }
+  unsigned int h = hash_key(key) & T.mask;
+  while (T.key[h] != key && T.key[h] != kEmptyKey) h = (h + 1) & T.mask;
+  slot_of[m] = h;
+}
+
+__global__ void mark_first(const unsigned int *__restrict__ first, const unsigned int *__restrict__ slot_of,
+                           int base, int n, unsigned int *flag)
+{
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int m = base + t;
   flag[m] = first[slot_of[m]] == (unsigned int)m ? 1u : 0u;
 }
 
@@ -484,13 +512,16 @@ __device__ __forceinline__ int resample_limit(int k, int min_samples, int max_sa
 }
 
 // n = min over m of (m+1) with (m+1) > limit(k_m)   (pf.c:483)
-__global__ void find_kld_cut(const unsigned int *__restrict__ k_inclusive, int count,
-                             int min_samples, int max_samples, double pop_err, double pop_z,
-                             int *cut)
+// Samples [base, base + count); k_m = k_offset + k_inclusive[m] (the offset is the
+// number of distinct bins first seen on lower ranks in a sharded run).
+__global__ void find_kld_cut(const unsigned int *__restrict__ k_inclusive, int base, int count,
+                             int k_offset, int min_samples, int max_samples, double pop_err,
+                             double pop_z, int *cut)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= count) return;
-  const int k = (int)k_inclusive[m];
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= count) return;
+  const int m = base + t;
+  const int k = k_offset + (int)k_inclusive[m];
   // limit() only changes where k changes, but evaluating it everywhere keeps
   // the kernel branch-free; min_samples gives a cheap early reject.
   if (m + 1 <= min_samples) return;
@@ -730,32 +761,25 @@ __global__ void cc_component_min(const BinTable T, unsigned int nslots, int n_va
   if (f < __ldcg(slot)) atomicMin(slot, f);
 }
 
-// a sample opens a new cluster when it is the earliest sample of its component
-__global__ void cc_mark_cluster_first(const BinTable T, const unsigned int *__restrict__ slot_of,
-                                      const unsigned int *__restrict__ flag, int n_valid,
-                                      const unsigned int *__restrict__ cmin, unsigned int *cflag)
+// Canonical cluster numbers: clusters are numbered in the order in which their
+// earliest sample appears.  Every root bin flags that sample's index; an
+// inclusive scan over sample indices ranks the flags; the root reads its rank
+// back.  Works on the table alone, so a sharded rank needs no other rank's
+// per-sample data.
+__global__ void cc_flag_roots(const BinTable T, unsigned int nslots, int n_valid,
+                              const unsigned int *__restrict__ cmin, unsigned int *cflag)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= n_valid) return;
-  unsigned int f = 0;
-  if (flag[m])
-  {
-    const unsigned int r = T.aux[slot_of[m]];   // root (set by cc_flatten)
-    f = cmin[r] == (unsigned int)m ? 1u : 0u;
-  }
-  cflag[m] = f;
+  const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (T.aux[s] == s) cflag[cmin[s]] = 1u;
 }
 
-// cluster id of a component = (number of cluster-opening samples before its
-// first sample); stored over cmin[root]
-__global__ void cc_assign_ids(const BinTable T, const unsigned int *__restrict__ slot_of,
-                              const unsigned int *__restrict__ cflag,
-                              const unsigned int *__restrict__ cscan, int n_valid, unsigned int *cid)
+__global__ void cc_assign_ids(const BinTable T, unsigned int nslots, int n_valid,
+                              const unsigned int *__restrict__ cscan, unsigned int *cmin_to_id)
 {
-  const int m = blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= n_valid || !cflag[m]) return;
-  const unsigned int r = T.aux[slot_of[m]];
-  cid[r] = cscan[m] - 1u;
+  const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (T.aux[s] == s) cmin_to_id[s] = cscan[cmin_to_id[s]] - 1u;   // cmin[root] -> cluster id
 }
 
 // ----------------------------------------------------------------- statistics --
@@ -1012,7 +1036,7 @@ static void sync_scalars(PfCtx *c, int first, int count)
 }
 
 // d_ints slots
-enum { I_DISTINCT = 0, I_CUT = 1, I_CLUSTERS = 2, I_OUTSIDE = 3, I_MOVED = 4 };
+enum { I_DISTINCT = 0, I_CUT = 1, I_CLUSTERS = 2, I_OUTSIDE = 3, I_MOVED = 4, I_KCUT = 5, I_RANKCNT = 24 };
 
 static void bin_sizes(const pf_sample_set_t *set, double *bx, double *by, double *bt)
 {
@@ -1061,16 +1085,16 @@ static void build_histogram(PfCtx *c, int count)
   }
   c->tab_dense = (count > 0 && cells <= (double)c->hash_cap) ? 1 : 0;
   if (c->tab_dense)
-    AMCL_CUDA(cudaMemsetAsync(c->d_tab_first, 0xFF, sizeof(unsigned int) * (size_t)cells, st));
+    AMCL_CUDA(cudaMemsetAsync(c->d_tab_first, 0x7F, sizeof(unsigned int) * (size_t)cells, st));
   else
   {
     AMCL_CUDA(cudaMemsetAsync(c->d_tab_key, 0xFF, sizeof(unsigned long long) * (size_t)c->hash_cap, st));
     AMCL_CUDA(cudaMemsetAsync(c->d_tab_first, 0xFF, sizeof(unsigned int) * (size_t)c->hash_cap, st));
   }
   const BinTable T = table_of(c);
-  bin_insert<<<blocks_for(count, 256), 256, 0, st>>>(c->d_keys, count, T, c->d_slot);
+  bin_insert<<<blocks_for(count, 256), 256, 0, st>>>(c->d_keys, 0, count, T, c->d_slot);
   AMCL_LAUNCH_CHECK();
-  mark_first<<<blocks_for(count, 256), 256, 0, st>>>(c->d_tab_first, c->d_slot, count, c->d_flag);
+  mark_first<<<blocks_for(count, 256), 256, 0, st>>>(c->d_tab_first, c->d_slot, 0, count, c->d_flag);
   AMCL_LAUNCH_CHECK();
 }
 
@@ -1129,10 +1153,11 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
   // cluster-opening flags reuse d_keys' storage as u32 scratch (keys are spent)
   unsigned int *cflag = reinterpret_cast<unsigned int *>(c->d_keys);
   unsigned int *cscan = cflag + c->alloc_samples;
-  cc_mark_cluster_first<<<nb, 256, 0, st>>>(T, c->d_slot, c->d_flag, n, cmin, cflag);
+  AMCL_CUDA(cudaMemsetAsync(cflag, 0, sizeof(unsigned int) * (size_t)(n > 0 ? n : 1), st));
+  cc_flag_roots<<<sb, 256, 0, st>>>(T, nslots, n, cmin, cflag);
   AMCL_LAUNCH_CHECK();
   scan_u32(c, cflag, cscan, n, I_CLUSTERS);
-  cc_assign_ids<<<nb, 256, 0, st>>>(T, c->d_slot, cflag, cscan, n, cmin);
+  cc_assign_ids<<<sb, 256, 0, st>>>(T, nslots, n, cscan, cmin);
   AMCL_LAUNCH_CHECK();
   sync_ints(c, I_CLUSTERS, 1);
   const int ncl = c->h_ints[I_CLUSTERS];
@@ -1462,30 +1487,123 @@ void run_resample(PfCtx *c)
   bin_sizes(set_b, &pa.bin_x, &pa.bin_y, &pa.bin_t);
   pick_and_copy<<<blocks_for(pa.count, 256), 256, 0, st>>>(pa);
   AMCL_LAUNCH_CHECK();
-  // ... and the bin keys of all candidates are exchanged: the KLD count below
-  // is a property of the global sample ORDER, so every rank evaluates it on the
-  // full key list and reaches the same n and k without further traffic.
-  if (sh.on())
-    sh.allgather(c->d_keys, (unsigned long long)sh.chunk(maxs) * sizeof(unsigned long long), sh.user);
-
   tr.mark("pick+keys");
   // ---- histogram, k_m, KLD cut ---------------------------------------------
-  build_histogram(c, maxs);
-  tr.mark("histogram");
-  scan_u32(c, c->d_flag, c->d_scan, maxs, I_DISTINCT);
-  c->h_ints[I_CUT] = maxs;
-  AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_CUT, c->h_ints + I_CUT, sizeof(int),
-                            cudaMemcpyHostToDevice, st));
-  find_kld_cut<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_scan, maxs, pf->min_samples, maxs,
-                                                      pf->pop_err, pf->pop_z, c->d_ints + I_CUT);
-  AMCL_LAUNCH_CHECK();
-  sync_ints(c, I_CUT, 1);
-  const int n = c->h_ints[I_CUT];
-  // leaf_count = k_{n-1}
+  // The KLD count is a property of the global sample ORDER: k_m = number of
+  // distinct bins among samples 0..m.
+  int n = maxs;
   unsigned int k_at_cut = 0;
-  AMCL_CUDA(cudaMemcpyAsync(&k_at_cut, c->d_scan + (n - 1), sizeof(unsigned int),
-                            cudaMemcpyDeviceToHost, st));
-  AMCL_CUDA(cudaStreamSynchronize(st));
+  bool shared_grid = false;
+  if (sh.on() && sh.world <= 32)
+  {
+    // Sharded, preferred way: agree on the key bounding box; if the dense grid
+    // fits, every rank enters only ITS samples and the grids are merged with one
+    // MIN all-reduce (23 MB for a 200 m map) instead of shipping 8 B per sample.
+    const int lo_c = sh.lo(maxs), cnt_c = sh.count(maxs);
+    int *h = c->h_ints + I_BOUNDS;
+    for (int q = 0; q < 3; q++) { h[q] = 0x7FFFFFFF; h[3 + q] = -0x7FFFFFFF; }
+    AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_BOUNDS, h, sizeof(int) * 6, cudaMemcpyHostToDevice, st));
+    if (cnt_c > 0)
+    {
+      int grid = globals().sm_count * 8;
+      if (grid > blocks_for(cnt_c, 256)) grid = blocks_for(cnt_c, 256);
+      key_bounds<<<grid, 256, 0, st>>>(c->d_keys + lo_c, cnt_c, c->d_ints + I_BOUNDS);
+      AMCL_LAUNCH_CHECK();
+    }
+    negate_ints<<<1, 32, 0, st>>>(c->d_ints + I_BOUNDS + 3, 3);      // max -> -max: one MIN serves all six
+    AMCL_LAUNCH_CHECK();
+    sh.allreduce(c->d_ints + I_BOUNDS, 6, SHARD_I32, SHARD_MIN, sh.user);
+    sync_ints(c, I_BOUNDS, 6);
+    double cells = 1.0;
+    for (int q = 0; q < 3; q++)
+    {
+      c->tab_lo[q] = h[q];
+      c->tab_ext[q] = -h[3 + q] - h[q] + 1;
+      cells *= (double)c->tab_ext[q];
+    }
+    shared_grid = cells <= (double)c->hash_cap;
+    if (shared_grid)
+    {
+      c->tab_dense = 1;
+      const BinTable T = table_of(c);
+      // 0x7F7F7F7F = empty: larger than any sample index, and positive as the
+      // int32 the all-reduce works on
+      AMCL_CUDA(cudaMemsetAsync(c->d_tab_first, 0x7F, sizeof(unsigned int) * (size_t)cells, st));
+      if (cnt_c > 0)
+      {
+        bin_insert<<<blocks_for(cnt_c, 256), 256, 0, st>>>(c->d_keys, lo_c, cnt_c, T, c->d_slot);
+        AMCL_LAUNCH_CHECK();
+      }
+      sh.allreduce(c->d_tab_first, (int)cells, SHARD_I32, SHARD_MIN, sh.user);
+      tr.mark("histogram");
+      // own flags, own inclusive scan, then the counts of the lower ranks
+      int *h_cnt = c->h_ints + I_RANKCNT;
+      for (int r = 0; r < sh.world; r++) h_cnt[r] = 0;
+      AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_RANKCNT, h_cnt, sizeof(int) * sh.world,
+                                cudaMemcpyHostToDevice, st));
+      if (cnt_c > 0)
+      {
+        mark_first<<<blocks_for(cnt_c, 256), 256, 0, st>>>(c->d_tab_first, c->d_slot, lo_c, cnt_c,
+                                                           c->d_flag);
+        AMCL_LAUNCH_CHECK();
+        scan_u32(c, c->d_flag + lo_c, c->d_scan + lo_c, cnt_c, I_RANKCNT + sh.rank);
+      }
+      sh.allreduce(c->d_ints + I_RANKCNT, sh.world, SHARD_I32, SHARD_SUM, sh.user);
+      sync_ints(c, I_RANKCNT, sh.world);
+      int k_offset = 0;
+      for (int r = 0; r < sh.rank; r++) k_offset += h_cnt[r];
+      c->h_ints[I_CUT] = maxs;
+      AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_CUT, c->h_ints + I_CUT, sizeof(int),
+                                cudaMemcpyHostToDevice, st));
+      if (cnt_c > 0)
+      {
+        find_kld_cut<<<blocks_for(cnt_c, 256), 256, 0, st>>>(c->d_scan, lo_c, cnt_c, k_offset,
+                                                             pf->min_samples, maxs, pf->pop_err,
+                                                             pf->pop_z, c->d_ints + I_CUT);
+        AMCL_LAUNCH_CHECK();
+      }
+      sh.allreduce(c->d_ints + I_CUT, 1, SHARD_I32, SHARD_MIN, sh.user);
+      sync_ints(c, I_CUT, 1);
+      n = c->h_ints[I_CUT];
+      // leaf_count = k_{n-1}, known to the rank whose slice holds sample n-1
+      c->h_ints[I_KCUT] = 0;
+      if (n - 1 >= lo_c && n - 1 < lo_c + cnt_c)
+      {
+        unsigned int local_k = 0;
+        AMCL_CUDA(cudaMemcpyAsync(&local_k, c->d_scan + (n - 1), sizeof(unsigned int),
+                                  cudaMemcpyDeviceToHost, st));
+        AMCL_CUDA(cudaStreamSynchronize(st));
+        c->h_ints[I_KCUT] = k_offset + (int)local_k;
+      }
+      AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_KCUT, c->h_ints + I_KCUT, sizeof(int),
+                                cudaMemcpyHostToDevice, st));
+      sh.allreduce(c->d_ints + I_KCUT, 1, SHARD_I32, SHARD_MAX, sh.user);
+      sync_ints(c, I_KCUT, 1);
+      k_at_cut = (unsigned int)c->h_ints[I_KCUT];
+    }
+  }
+  if (!shared_grid)
+  {
+    // One GPU, or the keys spread too far for a dense grid: every rank looks at
+    // the full key list (all-gathered when sharded) and reaches the same n and k.
+    if (sh.on())
+      sh.allgather(c->d_keys, (unsigned long long)sh.chunk(maxs) * sizeof(unsigned long long), sh.user);
+    build_histogram(c, maxs);
+    tr.mark("histogram");
+    scan_u32(c, c->d_flag, c->d_scan, maxs, I_DISTINCT);
+    c->h_ints[I_CUT] = maxs;
+    AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_CUT, c->h_ints + I_CUT, sizeof(int),
+                              cudaMemcpyHostToDevice, st));
+    find_kld_cut<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_scan, 0, maxs, 0, pf->min_samples, maxs,
+                                                        pf->pop_err, pf->pop_z, c->d_ints + I_CUT);
+    AMCL_LAUNCH_CHECK();
+    sync_ints(c, I_CUT, 1);
+    n = c->h_ints[I_CUT];
+    // leaf_count = k_{n-1}
+    AMCL_CUDA(cudaMemcpyAsync(&k_at_cut, c->d_scan + (n - 1), sizeof(unsigned int),
+                              cudaMemcpyDeviceToHost, st));
+    AMCL_CUDA(cudaStreamSynchronize(st));
+  }
   set_b->sample_count = n;
   set_b->kdtree->leaf_count = (int)k_at_cut;
   tr.mark("scan+cut");
@@ -1517,6 +1635,14 @@ void run_resample(PfCtx *c)
     pa.write_keys = 0;
     pick_and_copy<<<blocks_for(own_cnt, 256), 256, 0, st>>>(pa);
     AMCL_LAUNCH_CHECK();
+    if (shared_grid)
+    {
+      // this rank entered only its CANDIDATE slice into the grid; the samples of
+      // its new slice find their bins in the merged grid
+      bin_lookup<<<blocks_for(own_cnt, 256), 256, 0, st>>>(c->d_set[ib], own_lo, own_cnt, table_of(c),
+                                                          pa.bin_x, pa.bin_y, pa.bin_t, c->d_slot);
+      AMCL_LAUNCH_CHECK();
+    }
   }
   // pf.c:493-498: every weight is 1/n
   if (own_cnt > 0)
