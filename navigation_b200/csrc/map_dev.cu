@@ -136,8 +136,10 @@ MapCtx *map_ctx(map_t *map, bool create)
   m->scale = map->scale;
   m->origin_x = map->origin_x;
   m->origin_y = map->origin_y;
-  m->tiles_x = (m->sx + kTile - 1) / kTile;
-  m->tiles_y = (m->sy + kTile - 1) / kTile;
+  // one padding column and row (index sx / sy) hold the "off the map" code, so
+  // the sensor kernels clamp instead of branching
+  m->tiles_x = (m->sx + 1 + kTile - 1) / kTile;
+  m->tiles_y = (m->sy + 1 + kTile - 1) / kTile;
   m->btiles_x = (m->sx + 7) / 8;
   m->btiles_y = (m->sy + 7) / 8;
   size_t cells = (size_t)m->sx * m->sy;
@@ -311,7 +313,11 @@ edt_col_pass(const unsigned char *__restrict__ g, int sx, int sy, int R, int til
     const int tj = lj >> 2, ti = li >> 2;           // the quad is one row of one 4x4 tile
     uint16_t *o = s_out + (tj * (kPatchX / kTile) + ti) * 16 + (lj & 3) * 4;
 #pragma unroll
-    for (int b = 0; b < 4; b++) o[b] = (uint16_t)(best[b] > R2 ? R2 + 1 : best[b]);
+    for (int b = 0; b < 4; b++)
+    {
+      const bool inside = i0 + li + b < sx && j0 + lj < sy;
+      o[b] = (uint16_t)(!inside ? R2 + 2 : (best[b] > R2 ? R2 + 1 : best[b]));   // R2 + 2: off the map
+    }
   }
   __syncthreads();
   // (kPatchX/4) x (kPatchY/4) tiles of 32 bytes; a thread moves one 16-byte half
@@ -321,7 +327,7 @@ edt_col_pass(const unsigned char *__restrict__ g, int sx, int sy, int R, int til
     const int tile = q >> 1, part = q & 1;
     const int tj = tile / (kPatchX / kTile), ti = tile % (kPatchX / kTile);
     const int gi = (i0 >> 2) + ti, gj = (j0 >> 2) + tj;
-    if (gi * kTile >= sx || gj * kTile >= sy) continue;
+    if (gi >= tiles_x || gj * kTile > sy) continue;
     const uint4 *src = reinterpret_cast<const uint4 *>(s_out + tile * 16 + part * 8);
     uint4 *dst = reinterpret_cast<uint4 *>(code + ((size_t)gj * tiles_x + gi) * 16 + part * 8);
     *dst = *src;
@@ -426,7 +432,7 @@ void map_build_distance_codes(MapCtx *m, double max_occ_dist)
   dim3 g1((m->sx + 255) / 256, m->sy);
   edt_row_bits<<<g1, 256, 0, st>>>(m->d_rowbits, m->sx, m->sy, words, pad, R, m->d_rowdist);
   AMCL_LAUNCH_CHECK();
-  dim3 g2((m->sx + kPatchX - 1) / kPatchX, (m->sy + kPatchY - 1) / kPatchY);
+  dim3 g2((m->sx + 1 + kPatchX - 1) / kPatchX, (m->sy + 1 + kPatchY - 1) / kPatchY);  // + padding
   size_t smem = (((size_t)(kPatchY + 2 * R) * kPatchX + 15) & ~(size_t)15) +
                 (size_t)kPatchX * kPatchY * sizeof(uint16_t);
   if (smem > 48 * 1024)
@@ -474,7 +480,7 @@ void map_codes_from_host_cells(MapCtx *m)
   set_code_table(m, map->max_occ_dist);
   const int R2 = m->R * m->R;
   size_t ncodes = (size_t)m->tiles_x * m->tiles_y * 16;
-  std::vector<uint16_t> codes(ncodes, (uint16_t)(R2 + 1));
+  std::vector<uint16_t> codes(ncodes, (uint16_t)(R2 + 2));   // padding: off the map
   for (int j = 0; j < m->sy; j++)
     for (int i = 0; i < m->sx; i++)
     {

@@ -87,9 +87,9 @@ struct LfArgs
   const double *lut;        // code -> pz^3 (LF) | log pz (LFP); [ncodes_pad]
   const unsigned char *agree;  // code -> z < beam_skip_distance (COUNT mode)
   int ncodes_pad;
-  int code_offmap;          // table index used for off-map end points
-  const uint16_t *code;     // tiled distance codes
-  int tiles_x, sx, sy;
+  const uint16_t *code;     // tiled distance codes; column sx and row sy hold the off-map code
+  int sx, sy;
+  unsigned k_row, k_sub;    // 4*tiles_x and 4 - 4*tiles_x (mod 2^32; see cell_index)
   double lx, ly, la;        // laser pose in the robot frame
   double ox, oy, scale;     // map origin (centre) and resolution
   double half_x, half_y;    // 0.5 + size/2, folded into the cell coordinate
@@ -108,6 +108,14 @@ constexpr double kCellGuard = 536870912.0;  // 2^29: beyond this nothing is on a
 // gathers in flight per lane (ncu on the one-particle version: L1TEX 75 % busy,
 // half of it beam-table wavefronts; profiles/r1_ncu_full_likelihood_field_2M.md).
 constexpr int kBlockP = 4;
+
+// Offset of cell (mi, mj) in the 4x4-tiled code array,
+//   ((mj >> 2) * tiles_x + (mi >> 2)) * 16 + (mj & 3) * 4 + (mi & 3),
+// rewritten as a sum of products so that it is four multiply-adds and two ANDs.
+__device__ __forceinline__ unsigned cell_index(unsigned mi, unsigned mj, unsigned k_row, unsigned k_sub)
+{
+  return mi * 4u + mj * k_row - 3u * (mi & 3u) + k_sub * (mj & 3u);   // k_sub is negative mod 2^32
+}
 
 template <int MODE, bool LUT_IN_SMEM>
 __global__ void __launch_bounds__(kSensorThreads, 3)
@@ -142,9 +150,8 @@ likelihood_field_kernel(const LfArgs a)
   const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   const int warp_stride = gridDim.x * warps_per_block;
   const uint16_t *__restrict__ code = a.code;
-  const int tiles_x = a.tiles_x;
   const unsigned usx = (unsigned)a.sx, usy = (unsigned)a.sy;
-  const int offmap = a.code_offmap;
+  const unsigned k_row = a.k_row, k_sub = a.k_sub;
   double warp_total = 0.0;  // meaningful in lane 0
 
   for (int p0 = warp_global * kBlockP; p0 < a.n; p0 += warp_stride * kBlockP)
@@ -186,11 +193,12 @@ likelihood_field_kernel(const LfArgs a)
 #pragma unroll
       for (int q = 0; q < kBlockP; q++)
       {
-        const int mi = floor_to_int(fma(pc[q], b.x, fma(-ps[q], b.y, pX[q])));
-        const int mj = floor_to_int(fma(ps[q], b.x, fma(pc[q], b.y, pY[q])));
-        c[q] = offmap;
-        if ((unsigned)mi < usx && (unsigned)mj < usy)
-          c[q] = __ldg(code + ((((mj >> 2) * tiles_x + (mi >> 2)) << 4) | ((mj & 3) << 2) | (mi & 3)));
+        // !MAP_VALID end points (amcl_laser.cpp:283-286) -- negative indices wrap
+        // to huge unsigned values -- are clamped onto the padding column / row,
+        // whose cells hold the off-map code: no branch, no predicate.
+        const unsigned mi = min((unsigned)floor_to_int(fma(pc[q], b.x, fma(-ps[q], b.y, pX[q]))), usx);
+        const unsigned mj = min((unsigned)floor_to_int(fma(ps[q], b.x, fma(pc[q], b.y, pY[q]))), usy);
+        c[q] = __ldg(code + cell_index(mi, mj, k_row, k_sub));
       }
 #pragma unroll
       for (int q = 0; q < kBlockP; q++)
@@ -509,9 +517,12 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   a.lut = c->d_scan_tab + tab.size();
   a.agree = d_agree;
   a.ncodes_pad = ncodes_pad;
-  a.code_offmap = ncodes - 1;  // last entry: off-map end point
+  // last table entry = off-map end point = the code stored in the map's padding
+  if (ncodes - 1 != m->R * m->R + 2)
+    AMCL_FATAL("likelihood table has %d entries, the map's codes need %d", ncodes, m->R * m->R + 3);
   a.code = m->d_code;
-  a.tiles_x = m->tiles_x;
+  a.k_row = 4u * (unsigned)m->tiles_x;
+  a.k_sub = 4u - 4u * (unsigned)m->tiles_x;
   a.sx = m->sx;
   a.sy = m->sy;
   a.lx = laser_pose[0];
