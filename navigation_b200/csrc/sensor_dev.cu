@@ -89,7 +89,7 @@ struct LfArgs
   int ncodes_pad;
   const uint16_t *code;     // tiled distance codes; column sx and row sy hold the off-map code
   int sx, sy;
-  unsigned k_row, k_sub;    // 4*tiles_x and 4 - 4*tiles_x (mod 2^32; see cell_index)
+  unsigned k_row;           // 4 * tiles_x - 4 (see cell_index)
   double lx, ly, la;        // laser pose in the robot frame
   double ox, oy, scale;     // map origin (centre) and resolution
   double half_x, half_y;    // 0.5 + size/2, folded into the cell coordinate
@@ -110,11 +110,12 @@ constexpr double kCellGuard = 536870912.0;  // 2^29: beyond this nothing is on a
 constexpr int kBlockP = 4;
 
 // Offset of cell (mi, mj) in the 4x4-tiled code array,
-//   ((mj >> 2) * tiles_x + (mi >> 2)) * 16 + (mj & 3) * 4 + (mi & 3),
-// rewritten as a sum of products so that it is four multiply-adds and two ANDs.
-__device__ __forceinline__ unsigned cell_index(unsigned mi, unsigned mj, unsigned k_row, unsigned k_sub)
+//   ((mj >> 2) * tiles_x + (mi >> 2)) * 16 + (mj & 3) * 4 + (mi & 3).
+// With t = mi & ~3 and u = mj & ~3 this is (3 t + mi) + (k_row u + 4 mj),
+// k_row = 4 tiles_x - 4: two ANDs, two multiply-adds and one shift-add.
+__device__ __forceinline__ unsigned cell_index(unsigned mi, unsigned mj, unsigned k_row)
 {
-  return mi * 4u + mj * k_row - 3u * (mi & 3u) + k_sub * (mj & 3u);   // k_sub is negative mod 2^32
+  return (mi & ~3u) * 3u + mi + (mj & ~3u) * k_row + (mj << 2);
 }
 
 template <int MODE, bool LUT_IN_SMEM>
@@ -151,7 +152,7 @@ likelihood_field_kernel(const LfArgs a)
   const int warp_stride = gridDim.x * warps_per_block;
   const uint16_t *__restrict__ code = a.code;
   const unsigned usx = (unsigned)a.sx, usy = (unsigned)a.sy;
-  const unsigned k_row = a.k_row, k_sub = a.k_sub;
+  const unsigned k_row = a.k_row;
   double warp_total = 0.0;  // meaningful in lane 0
 
   for (int p0 = warp_global * kBlockP; p0 < a.n; p0 += warp_stride * kBlockP)
@@ -198,7 +199,7 @@ likelihood_field_kernel(const LfArgs a)
         // whose cells hold the off-map code: no branch, no predicate.
         const unsigned mi = min((unsigned)floor_to_int(fma(pc[q], b.x, fma(-ps[q], b.y, pX[q]))), usx);
         const unsigned mj = min((unsigned)floor_to_int(fma(ps[q], b.x, fma(pc[q], b.y, pY[q]))), usy);
-        c[q] = __ldg(code + cell_index(mi, mj, k_row, k_sub));
+        c[q] = __ldg(code + cell_index(mi, mj, k_row));
       }
 #pragma unroll
       for (int q = 0; q < kBlockP; q++)
@@ -521,8 +522,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   if (ncodes - 1 != m->R * m->R + 2)
     AMCL_FATAL("likelihood table has %d entries, the map's codes need %d", ncodes, m->R * m->R + 3);
   a.code = m->d_code;
-  a.k_row = 4u * (unsigned)m->tiles_x;
-  a.k_sub = 4u - 4u * (unsigned)m->tiles_x;
+  a.k_row = 4u * (unsigned)m->tiles_x - 4u;
   a.sx = m->sx;
   a.sy = m->sy;
   a.lx = laser_pose[0];

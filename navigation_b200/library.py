@@ -11,7 +11,8 @@ import subprocess
 from . import abi
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libamcl_b200.so")
+# AMCLB200_LIB names another build of the same library (kernel-variant experiments)
+LIB_PATH = os.environ.get("AMCLB200_LIB") or os.path.join(HERE, "lib", "libamcl_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 
 _lib = None
