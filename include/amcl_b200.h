@@ -135,6 +135,31 @@ void amclb200_pf_load_device(pf_t *pf, const void *d_particles, int n);
  * mean and covariance of the heaviest cluster of the current set; -1 if none. */
 int amclb200_pf_best_cluster(pf_t *pf, double *weight, pf_vector_t *mean, pf_matrix_t *cov);
 
+/* ---- the data formats either side of the filter (N2, N4) -----------
+ *
+ * Map ingest: map_server's image -> occupancy rule
+ * (map_server/src/image_loader.cpp:57-165: channel mean, negate, occupied / free
+ * thresholds, modes 0 = TRINARY, 1 = SCALE, 2 = RAW, rows flipped so that cell
+ * (0,0) is the lower-left pixel) fused with AmclNode::convertMap
+ * (amcl/src/amcl_node.cpp:987-1012: 0 -> free, 100 -> occupied, anything else
+ * unknown; origin moved to the map centre).  `pixels` are DECODED image bytes
+ * as SDL hands them over (rowstride = pitch, n_channels = BytesPerPixel,
+ * has_alpha_mask = format->Amask != 0); origin is the yaml's [x, y, yaw].
+ * Returns a map_t (free with map_free) whose occupancy is already resident on
+ * the device; grid_out, if not NULL, receives the width*height OccupancyGrid
+ * bytes map_server would have published. */
+map_t *amclb200_map_from_image(const unsigned char *pixels, int width, int height, int rowstride,
+                               int n_channels, int has_alpha_mask, double resolution,
+                               const double origin[3], int negate, double occ_th, double free_th,
+                               int mode, signed char *grid_out);
+
+/* The particle cloud AmclNode publishes (amcl_node.cpp:1349-1362): every
+ * `stride`-th sample of the current set as 7 doubles -- position x, y, 0 and the
+ * quaternion x, y, z, w of tf2::Quaternion::setRPY(0, 0, yaw) -- packed on the
+ * device; only these bytes are copied to `out` (host).  Returns the number of
+ * poses written (<= max_poses). */
+int amclb200_pf_pack_cloud(pf_t *pf, int stride, int max_poses, double *out);
+
 /* ---- several GPUs, one process each -------------------------------------------
  * Collectives are supplied by the host program (torch.distributed / NCCL in
  * bench.py).  Both act IN PLACE on DEVICE buffers and must be ordered with the

@@ -10,6 +10,7 @@
 #pragma once
 
 #include <stdint.h>
+#include <functional>
 #include <utility>
 #include <vector>
 
@@ -78,6 +79,8 @@ struct MapCtx
 MapCtx *map_ctx(map_t *map, bool create);
 void map_ctx_release(map_t *map);
 void map_upload_occupancy(MapCtx *m);            // host cells -> d_occ, d_blocked
+void map_finish_occupancy_on_device(MapCtx *m);  // d_occ already written on the device -> d_blocked
+void parallel_rows(int rows, const std::function<void(int, int)> &body);  // host row loops on several cores
 void map_build_distance_codes(MapCtx *m, double max_occ_dist);  // exact EDT
 void map_codes_to_host_cells(MapCtx *m);         // fills cells[].occ_dist
 void map_codes_from_host_cells(MapCtx *m);       // encodes cells[].occ_dist
@@ -171,6 +174,8 @@ struct PfCtx
   double *d_scan_tab = nullptr;
   int scan_tab_cap = 0;
   double *d_skip = nullptr;       // beam-skip pass: per-beam agreement counts + code->agree bytes
+  double *d_cloud = nullptr;      // packed PoseArray for the caller (amclb200_pf_pack_cloud)
+  size_t cloud_cap = 0;
   int skip_cap = 0;
 
   uint64_t step = 0;              // counter feeding the Philox key

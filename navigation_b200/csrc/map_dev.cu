@@ -339,7 +339,7 @@ edt_col_pass(const unsigned char *__restrict__ g, int sx, int sy, int R, int til
 // The caller's grid is an array of 16-byte structs; converting 16 M of them to
 // and from the packed device formats is host-memory bound, so the row loops are
 // spread over the host cores.
-static void parallel_rows(int rows, const std::function<void(int, int)> &body)
+void parallel_rows(int rows, const std::function<void(int, int)> &body)
 {
   unsigned hw = std::thread::hardware_concurrency();
   int nt = (int)(hw ? (hw > 16 ? 16 : hw) : 4);
@@ -385,6 +385,18 @@ void map_upload_occupancy(MapCtx *m)
                                                          m->btiles_y, m->d_blocked);
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaStreamSynchronize(st));  // occ is a stack-lifetime staging buffer
+  m->occ_uploaded = true;
+}
+
+// d_occ was written by a kernel (amclb200_map_from_image): derive the
+// ray-casting bit tiles from it and mark the occupancy as resident.
+void map_finish_occupancy_on_device(MapCtx *m)
+{
+  cudaStream_t st = globals().stream;
+  int nt = m->btiles_x * m->btiles_y;
+  build_blocked_bits<<<(nt + 255) / 256, 256, 0, st>>>(m->d_occ, m->sx, m->sy, m->btiles_x,
+                                                         m->btiles_y, m->d_blocked);
+  AMCL_LAUNCH_CHECK();
   m->occ_uploaded = true;
 }
 

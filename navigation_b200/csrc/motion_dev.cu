@@ -39,7 +39,16 @@ struct MotionArgs
   int offset;                // global index of set[0] (sharded runs own a slice)
 };
 
-__device__ __forceinline__ double wrap_angle(double z) { return atan2(sin(z), cos(z)); }
+// normalize() of amcl_odom.cpp:38-42, atan2(sin z, cos z).  For |z| <= 3 (< pi)
+// the mathematical result is z itself and the reference's libm chain returns it
+// to within an ulp or two, the same size as the difference between host and
+// device libm; those angles (every noise sample, in practice) skip the three
+// transcendental calls.
+__device__ __forceinline__ double wrap_angle(double z)
+{
+  if (fabs(z) <= 3.0) return z;
+  return atan2(sin(z), cos(z));
+}
 
 // amcl_odom.cpp:44-58 with the first argument already wrapped on the host.
 __device__ __forceinline__ double angle_diff_wrapped_a(double a_wrapped, double b)

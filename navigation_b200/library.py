@@ -49,6 +49,10 @@ EXTENSION_SYMBOLS = {
     "amclb200_measure_gather_rate": (C.c_double, [C.c_uint64, C.c_int]),
     "amclb200_edt_codes_static": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "amclb200_edt_static_max_cells": (C.c_uint64, []),
+    "amclb200_map_from_image": (abi.map_p, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
+                                            C.POINTER(C.c_double), C.c_int, C.c_double, C.c_double, C.c_int,
+                                            C.c_void_p]),
+    "amclb200_pf_pack_cloud": (C.c_int, [abi.pf_p, C.c_int, C.c_int, C.c_void_p]),
 }
 
 RNG_PHILOX, RNG_DRAND48 = 0, 1

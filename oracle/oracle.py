@@ -85,6 +85,10 @@ def port():
         "orc_update_converged": (C.c_int, [f64p, C.c_int, C.c_double]),
         "orc_cep_stats": (None, [f64p, C.c_int, f64p]),
         "orc_bin_first_occurrence": (C.c_int, [f64p, C.c_int, i32p]),
+        "orc_image_to_grid": (None, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                     C.c_double, C.c_double, C.c_int, C.c_void_p]),
+        "orc_convert_map": (None, [C.c_void_p, C.c_size_t, i8p]),
+        "orc_pack_cloud": (C.c_int, [f64p, C.c_int, C.c_int, C.c_int, f64p]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -158,3 +162,36 @@ def occ_dist_from_d2(d2, scale, max_occ_dist):
     out = np.empty(d2.shape, dtype=np.float64)
     port().orc_d2_to_occ_dist(np.ascontiguousarray(d2), d2.size, scale, max_occ_dist, out)
     return out
+
+
+# ---- either side of the filter (node_io_oracle.c) ---------------------------------
+MAP_MODES = {"trinary": 0, "scale": 1, "raw": 2}
+
+
+def image_to_grid(pixels, negate=False, occ_th=0.65, free_th=0.196, mode="trinary", has_alpha_mask=None):
+    """map_server's loader on decoded pixels (h, w) or (h, w, channels) uint8 -> int8 grid (h, w), bottom row first."""
+    px = np.ascontiguousarray(pixels, dtype=np.uint8)
+    h, w = px.shape[:2]
+    ch = 1 if px.ndim == 2 else px.shape[2]
+    if has_alpha_mask is None:
+        has_alpha_mask = ch in (2, 4)
+    grid = np.empty((h, w), dtype=np.int8)
+    port().orc_image_to_grid(px.ctypes.data, w, h, w * ch, ch, int(has_alpha_mask), int(negate),
+                             occ_th, free_th, MAP_MODES[mode], grid.ctypes.data)
+    return grid
+
+
+def convert_map(grid):
+    g = np.ascontiguousarray(grid, dtype=np.int8)
+    out = np.empty(g.shape, dtype=np.int8)
+    port().orc_convert_map(g.ctypes.data, g.size, out)
+    return out
+
+
+def pack_cloud(samples, stride=1, max_poses=None):
+    s = np.ascontiguousarray(samples, dtype=np.float64)
+    n = s.shape[0]
+    cap = (n + stride - 1) // stride if max_poses is None else max_poses
+    out = np.empty((max(cap, 1), 7), dtype=np.float64)
+    cnt = port().orc_pack_cloud(s, n, stride, cap, out)
+    return out[:cnt]
