@@ -160,6 +160,27 @@ map_t *amclb200_map_from_image(const unsigned char *pixels, int width, int heigh
  * poses written (<= max_poses). */
 int amclb200_pf_pack_cloud(pf_t *pf, int stride, int max_poses, double *out);
 
+/* Costmap inflation (N3): costmap_2d::InflationLayer::updateCosts
+ * (costmap_2d/plugins/inflation_layer.cpp:176-263) on a caller-owned cost grid
+ * (row-major unsigned char, x fastest, cost_values.h encoding), in place.  The
+ * window [min_i, max_i) x [min_j, max_j) is the layer's update window BEFORE it
+ * is grown by the inflation radius; resolution, inscribed_radius,
+ * inflation_radius and cost_scaling_factor are the layer's resolution_,
+ * inscribed_radius_, inflation_radius_ and weight_.  Every cell within the cell
+ * radius of a LETHAL_OBSTACLE cell of the grown window gets
+ * max(old, computeCost(distance to the nearest such cell)), with the
+ * NO_INFORMATION / inflate_unknown rule of :253-256.  `costs` is a host pointer
+ * (only the rows the update can touch are copied each way) or, with on_device
+ * != 0, a device pointer.  Returns the number of cells visited (0 when the cell
+ * radius is 0, as the reference returns early). */
+int amclb200_inflate_costs(unsigned char *costs, int on_device, int size_x, int size_y, int min_i,
+                           int min_j, int max_i, int max_j, double resolution,
+                           double inscribed_radius, double inflation_radius,
+                           double cost_scaling_factor, int inflate_unknown);
+
+/* Device time (ms) of the three kernels of the last amclb200_inflate_costs call. */
+float amclb200_inflate_last_ms(void);
+
 /* ---- several GPUs, one process each -------------------------------------------
  * Collectives are supplied by the host program (torch.distributed / NCCL in
  * bench.py).  Both act IN PLACE on DEVICE buffers and must be ordered with the

@@ -89,6 +89,10 @@ def port():
                                      C.c_double, C.c_double, C.c_int, C.c_void_p]),
         "orc_convert_map": (None, [C.c_void_p, C.c_size_t, i8p]),
         "orc_pack_cloud": (C.c_int, [f64p, C.c_int, C.c_int, C.c_int, f64p]),
+        "orc_inflation_cost": (C.c_ubyte, [C.c_double] * 4),
+        "orc_cell_distance": (C.c_uint, [C.c_double, C.c_double]),
+        "orc_inflate": (None, [C.c_void_p] + [C.c_int] * 6 + [C.c_double] * 4 + [C.c_int]),
+        "orc_inflate_exact": (None, [C.c_void_p] + [C.c_int] * 6 + [C.c_double] * 4 + [C.c_int]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -195,3 +199,16 @@ def pack_cloud(samples, stride=1, max_poses=None):
     out = np.empty((max(cap, 1), 7), dtype=np.float64)
     cnt = port().orc_pack_cloud(s, n, stride, cap, out)
     return out[:cnt]
+
+
+def inflate(master, window=None, resolution=1.0, inscribed_radius=0.0, inflation_radius=0.55,
+            weight=10.0, inflate_unknown=False, exact=False):
+    """InflationLayer::updateCosts on a (size_y, size_x) uint8 cost grid; returns a new grid.
+    window = (min_i, min_j, max_i, max_j), default the whole map."""
+    g = np.array(master, dtype=np.uint8, order="C", copy=True)
+    sy, sx = g.shape
+    w = (0, 0, sx, sy) if window is None else window
+    fn = port().orc_inflate_exact if exact else port().orc_inflate
+    fn(g.ctypes.data, sx, sy, w[0], w[1], w[2], w[3], resolution, inscribed_radius, inflation_radius,
+       weight, int(inflate_unknown))
+    return g
