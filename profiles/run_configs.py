@@ -108,8 +108,36 @@ def edt_case(size):
                 hbm_frac=(3 * size * size / (t_k * 1e-3) / 1e9 / HBM) if t_k else None)
 
 
+def inflation_case(size):
+    """N3: InflationLayer::updateCosts over the whole K3 map (costmap defaults: radius 0.55 m, weight 10)."""
+    from oracle import oracle
+    occ = synth.rooms_map(size, seed=1)
+    g = np.where(occ == 1, 254, 0).astype(np.uint8)
+    d = torch.from_numpy(g).cuda()
+    pristine = d.clone()
+
+    def dev():
+        d.copy_(pristine)
+        lib.amclb200_inflate_costs(d.data_ptr(), 1, size, size, 0, 0, size, size, 0.05, 0.2, 0.55, 10.0, 0)
+
+    t_dev_call = timed(dev)
+    t_k = lib.amclb200_inflate_last_ms()
+    h = g.copy()
+    t_host_call = timed(lambda: lib.amclb200_inflate_costs(h.ctypes.data, 0, size, size, 0, 0, size, size,
+                                                           0.05, 0.2, 0.55, 10.0, 0), reps=3, warm=1)
+    sub = 1000
+    t0 = time.perf_counter()
+    oracle.inflate(g[:sub, :sub], None, 0.05, 0.2, 0.55, 10.0)
+    t_cpu = (time.perf_counter() - t0) * 1e3 * (size / sub) ** 2
+    return dict(config="N3 inflation %d^2, radius 11 cells" % size, map=size, kernels_ms=t_k,
+                device_call_ms=t_dev_call, host_call_ms=t_host_call,
+                cpu_sweep_ms_scaled_from_1000sq=t_cpu, algorithmic_bytes=2 * size * size,
+                hbm_frac=2 * size * size / (t_k * 1e-3) / 1e9 / HBM)
+
+
 def main():
     res = []
+    res.append(inflation_case(4000))
     res.append(sensor_case("K1 likelihood_field 5000 x 180, 1000^2", 1000, 5000, 180, "lf", resample=True))
     res.append(sensor_case("K2 beam 100k x 360, 2000^2", 2000, 100000, 360, "beam"))
     res.append(edt_case(2000))

@@ -42,7 +42,11 @@ def main():
         side = Side(lib, occ)
         side.alloc(100, n, pop_err=0.01, pop_z=0.99)
         lib.amclb200_set_mirror(side.pf, 0)
-        side.make_laser(beams, model="lf")
+        model = os.environ.get("SHARD_MODEL", "lf")       # lf | lfp | lfp_skip | beam
+        if model == "lfp_skip":
+            side.make_laser(beams, model="lfp", beamskip=(1, 0.5, 0.3, 0.9))
+        else:
+            side.make_laser(beams, model=model)
         side.make_odom(model=abi.ODOM_MODEL_DIFF)
         bear = synth.scan_bearings(beams)
         rays = np.stack([np.full_like(bear, pose[0]), np.full_like(bear, pose[1]), pose[2] + bear], 1).copy()
@@ -52,12 +56,19 @@ def main():
         cloud = synth.uniform_cloud(occ, 0.05, n, 9)
         cloud[: n // 3] = synth.gaussian_cloud(pose, (0.4, 0.4, 0.2), n // 3, 5)
         cloud[:, 3] = 1.0 / n
+        if model == "lfp_skip":
+            # beam skipping needs a converged set (amcl_laser.cpp:342): a tight cloud
+            cloud = synth.gaussian_cloud(pose, (0.05, 0.05, 0.05), n, 5)
+            cloud[:, 3] = 1.0 / n
         if mode == "sharded":
             coll.attach(lib, side.pf, peer_access=os.environ.get("SHARD_P2P", "1") == "1")
         side.set_samples(cloud)            # replicated start on every rank
         log = []
         for step in range(3):
             side.update_action((0.1 * step, 0.0, 0.02), (0.1, 0.0, 0.02))
+            if model == "lfp_skip":
+                side.cur.converged = 1
+                side.pf.contents.converged = 1
             side.update_sensor(scan, 30.0)
             neff = side.cur.n_effective
             side.resample()
