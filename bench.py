@@ -352,8 +352,9 @@ def b200_arm(args):
         "note": ("algorithmic bytes = 32 B per evaluation (one L2 sector per uncorrelated gather) + 40 B per "
                  "particle (SURVEY.md 8d); the map is L2-resident, so HBM is not the binding bound: DRAM "
                  "traffic ('traffic', ncu) is ~64 B per particle.  Neighbouring beams share sectors, which "
-                 "is why achieved exceeds the uncorrelated-gather peak; the kernel itself is L1TEX-bound "
-                 "(75 % of peak, ncu)"),
+                 "is why achieved exceeds the uncorrelated-gather peak; ncu: L1TEX 90 %, issue 61 %, fp64 pipe "
+                 "41 %; ablations (profiles/r1_ncu_full_likelihood_field_16M_v2.md) put the arithmetic alone at "
+                 "15.2 ms of the 18.3 ms"),
         "evals_per_s": k_evals / (k_ms * 1e-3), "gather_peak_per_s": gather_rate,
         "kernel_ms": k_ms, "share_of_step": k_ms / ms_step,
         "peak_source": "measured live: uncorrelated 2-byte gathers over a %d MB table (one 32-B sector each)" % (map_bytes >> 20),
