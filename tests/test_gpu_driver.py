@@ -87,3 +87,45 @@ def test_tracking_run_matches_truth_and_reference(gpu_lib, ref):
     for (pg, _, ng), (pr, _, nr) in zip(est_gpu, est_ref):
         assert ng == nr                                   # KLD sample counts step by step
         assert np.allclose(pg, pr, rtol=0, atol=1e-6)
+
+
+def test_flat_file_replay_equals_in_memory_run(gpu_lib, tmp_path):
+    """runFromBag's role (amcl_node.cpp:676-766): a run written to a flat file and
+    replayed from it gives the same estimates as feeding the scans directly."""
+    from navigation_b200 import replay
+
+    gpu_lib.amclb200_set_rng(library.RNG_DRAND48, 0)
+    occ = synth.rooms_map(400, seed=3)
+    bag, bear = driver.simulate_run(gpu_lib, occ, 0.05, _path(), n_beams=60, seed=1)
+    path = str(tmp_path / "run.npz")
+    replay.save_log(path, bag, bear, 12.0, occ=occ, scale=0.05)
+    log = replay.load_log(path)
+    assert log["ranges"].shape == (len(bag), 60)
+    params = dict(min_particles=500, max_particles=3000, laser_max_beams=30, alpha_slow=0.0, alpha_fast=0.0,
+                  init_pose=(2.6, 2.4, 0.05), init_cov=(0.1, 0.1, 0.03), d_thresh=0.2, a_thresh=0.2,
+                  resample_interval=1)
+    libc = C.CDLL(None)
+    libc.srand48.argtypes = [C.c_long]
+    gpu_lib.amclb200_set_reseed(0)
+    libc.srand48(5)
+    track, updates = replay.replay(gpu_lib, log, **params)
+    libc.srand48(5)
+    est, up2, _ = _run_plain(gpu_lib, bag, bear, occ, params)
+    gpu_lib.amclb200_set_reseed(1)
+    assert updates == up2 and len(track) == len(est)
+    assert np.allclose(np.array([t["pose"] for t in track]), np.array(est), rtol=0, atol=1e-12)
+    err, aerr = replay.score(track)
+    assert err < 0.25 and aerr < 0.15
+
+
+def _run_plain(lib, bag, bear, occ, params):
+    d = driver.AmclDriver(lib, occ, **params)
+    inc = bear[1] - bear[0]
+    est = []
+    for odom, ranges, truth in bag:
+        out = d.laser_received(odom, ranges, bear[0], inc, 0.0, 12.0)
+        if out["pose"] is not None:
+            est.append(out["pose"])
+    up = d.updates
+    d.close()
+    return est, up, None
