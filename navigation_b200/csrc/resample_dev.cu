@@ -687,7 +687,22 @@ cc_brick_local(const BinTable T, int bricks_x, int bricks_y, int n_valid, unsign
           (unsigned)nt >= (unsigned)kBrickT)
         continue;
       const unsigned int nb = (unsigned int)((nt * kBrickY + ny) * kBrickX + nx);
-      if (s_occ[nb]) suf_union(s_lab, threadIdx.x, nb);
+      if (!s_occ[nb]) continue;
+      // A diagonal link is implied when a cell "between" the two -- the
+      // neighbour with one of the offset's components set back to zero -- is
+      // occupied: that cell is a face neighbour of nb and a less diagonal
+      // neighbour of this cell, so by induction on the number of non-zero
+      // components the face links alone already connect them.  (Only cells of
+      // this brick are consulted here; cc_brick_borders applies the same rule
+      // with the global occupancy.)
+      bool implied = false;
+      if ((dx != 0) + (dy != 0) + (dt != 0) >= 2)
+      {
+        if (dx != 0 && s_occ[(nt * kBrickY + ny) * kBrickX + lx]) implied = true;
+        if (dy != 0 && s_occ[(nt * kBrickY + ly) * kBrickX + nx]) implied = true;
+        if (dt != 0 && s_occ[(lt * kBrickY + ny) * kBrickX + nx]) implied = true;
+      }
+      if (!implied) suf_union(s_lab, threadIdx.x, nb);
     }
   }
   __syncthreads();
@@ -728,7 +743,16 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid)
     if ((unsigned)nx >= (unsigned)T.ex || (unsigned)ny >= (unsigned)T.ey || (unsigned)nt >= (unsigned)T.et)
       continue;
     const unsigned int nb = (unsigned int)((nt * T.ey + ny) * T.ex + nx);
-    if (T.first[nb] < (unsigned int)n_valid) uf_union(T.aux, s, nb);
+    if (T.first[nb] >= (unsigned int)n_valid) continue;
+    // same pruning as in cc_brick_local, now with any cell of the grid in between
+    bool implied = false;
+    if ((dx != 0) + (dy != 0) + (dt != 0) >= 2)
+    {
+      if (dx != 0 && T.first[(nt * T.ey + ny) * T.ex + ix] < (unsigned int)n_valid) implied = true;
+      if (!implied && dy != 0 && T.first[(nt * T.ey + iy) * T.ex + nx] < (unsigned int)n_valid) implied = true;
+      if (!implied && dt != 0 && T.first[(it * T.ey + ny) * T.ex + nx] < (unsigned int)n_valid) implied = true;
+    }
+    if (!implied) uf_union(T.aux, s, nb);
   }
 }
 
