@@ -275,8 +275,61 @@ __global__ void sample_table(const double *__restrict__ cum, int n_coarse, doubl
   if (j < n_coarse) coarse[j] = cum[(size_t)(j + 1) * kCoarse];
 }
 
+// #{ j in 1..n : cum[j] <= r }, searched inside [lo, hi] (the caller knows that
+// cum[j] <= r for j <= lo and cum[j] > r for j > hi).
+__device__ __forceinline__ int table_rank_between(const double *__restrict__ cum, double r, int lo, int hi)
+{
+  while (lo < hi)
+  {
+    const int mid = lo + ((hi - lo) >> 1);
+    if (cum[mid + 1] <= r) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+
+// The same count over the whole table, through the coarse level when present:
+// every kCoarse-th entry lives in a small array that stays in L1/L2, so only
+// the last ~8 probes touch the big table.
+__device__ __forceinline__ int table_rank(const double *__restrict__ coarse, int n_coarse,
+                                          const double *__restrict__ cum, int n, double r)
+{
+  int lo = 0, hi = n;
+  if (coarse)
+  {
+    int clo = 0, chi = n_coarse;   // #{ j in 1..n_coarse : cum[j*kCoarse] <= r }
+    while (clo < chi)
+    {
+      const int mid = clo + ((chi - clo) >> 1);
+      if (__ldg(coarse + mid) <= r) clo = mid + 1;
+      else chi = mid;
+    }
+    lo = clo * kCoarse;
+    hi = min(n, lo + kCoarse - 1);
+    // entries lo+1 .. lo+kCoarse-1 are undecided; cum[lo+kCoarse] > r is known
+  }
+  return table_rank_between(cum, r, lo, hi);
+}
+
+// Bucket index of the table: index[b] = #{ j : cum[j] <= b / buckets } for
+// b = 0..buckets (buckets is a power of two, so b / buckets and r * buckets are
+// exact).  A draw r in [b/buckets, (b+1)/buckets) then has its answer inside
+// [index[b], index[b+1]] -- a handful of neighbouring entries instead of a
+// 24-level search through 128 MB.  Built with one full search per bucket,
+// 1/16 of the searches the draws themselves would need.
+__global__ void build_bucket_index(const double *__restrict__ coarse, int n_coarse,
+                                   const double *__restrict__ cum, int n, int buckets,
+                                   int *__restrict__ index)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > buckets) return;
+  index[b] = table_rank(coarse, n_coarse, cum, n, (double)b / (double)buckets);
+}
+
 struct PickArgs
 {
+  const int *bucket_index;  // see build_bucket_index, or null
+  int buckets;
   const double *coarse;     // every kCoarse-th table entry, or null
   int n_coarse;
   const Particle *src;
@@ -311,28 +364,15 @@ __global__ void pick_and_copy(const PickArgs a)
   else
   {
     const double r = a.draws[2 * (size_t)m + 1];
-    int lo = 0, hi = a.n_src;  // answer = #{ i in 1..n : cum[i] <= r }
-    // Coarse level first: every kCoarse-th table entry lives in a small array
-    // that stays in L1/L2, so only the last ~8 probes touch the big table.
-    if (a.coarse)
+    int lo;
+    if (a.bucket_index)
     {
-      int clo = 0, chi = a.n_coarse;   // #{ j in 1..n_coarse : cum[j*kCoarse] <= r }
-      while (clo < chi)
-      {
-        const int mid = clo + ((chi - clo) >> 1);
-        if (__ldg(a.coarse + mid) <= r) clo = mid + 1;
-        else chi = mid;
-      }
-      lo = clo * kCoarse;
-      hi = min(a.n_src, lo + kCoarse - 1);
-      // entries lo+1 .. lo+kCoarse-1 are undecided; cum[lo+kCoarse] > r is known
+      const int b = min((int)(r * (double)a.buckets), a.buckets - 1);   // r < 1
+      const int2 range = make_int2(__ldg(a.bucket_index + b), __ldg(a.bucket_index + b + 1));
+      lo = table_rank_between(a.cum, r, range.x, min(range.y, a.n_src));
     }
-    while (lo < hi)
-    {
-      const int mid = lo + ((hi - lo) >> 1);
-      if (a.cum[mid + 1] <= r) lo = mid + 1;
-      else hi = mid;
-    }
+    else
+      lo = table_rank(a.coarse, a.n_coarse, a.cum, a.n_src, r);
     if (lo >= a.n_src) lo = a.n_src - 1;  // r beyond the table's last entry
     from = lo;
     // the owner's copy is the current one; a remote owner is read over NVLink
@@ -1497,6 +1537,24 @@ void run_resample(PfCtx *c)
     sample_table<<<blocks_for(pa.n_coarse, 256), 256, 0, st>>>(c->d_cum, pa.n_coarse, c->d_partials);
     AMCL_LAUNCH_CHECK();
     pa.coarse = c->d_partials;
+  }
+  pa.bucket_index = nullptr;
+  pa.buckets = 0;
+  if (n_a >= (1 << 16))
+  {
+    int buckets = 1;
+    while (buckets * 16 < n_a) buckets <<= 1;     // about 16 table entries per bucket
+    if ((size_t)buckets + 1 > c->bucket_cap)
+    {
+      if (c->d_bucket_index) cudaFree(c->d_bucket_index);
+      c->bucket_cap = (size_t)buckets + 1;
+      AMCL_CUDA(cudaMalloc(&c->d_bucket_index, sizeof(int) * c->bucket_cap));
+    }
+    build_bucket_index<<<blocks_for(buckets + 1, 256), 256, 0, st>>>(pa.coarse, pa.n_coarse, c->d_cum, n_a,
+                                                                     buckets, c->d_bucket_index);
+    AMCL_LAUNCH_CHECK();
+    pa.bucket_index = c->d_bucket_index;
+    pa.buckets = buckets;
   }
   pa.draws = c->d_draws;
   pa.injected = d_injected;

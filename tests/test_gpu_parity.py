@@ -292,7 +292,9 @@ def _check_resample_against_oracle(lib, port, occ, cloud, min_s, pop_err, pop_z,
 
 
 @pytest.mark.parametrize("kind,n,seed", [("tracking", 20000, 1), ("global", 20000, 2),
-                                         ("global", 3000, 3), ("tracking", 777, 4)])
+                                         ("global", 3000, 3), ("tracking", 777, 4),
+                                         # >= 65536 source samples: the bucket index of the table is used
+                                         ("global", 150000, 5), ("spiky", 100000, 6), ("tracking", 70001, 7)])
 def test_resample_bit_exact_vs_oracle(lib, port, kind, n, seed):
     occ = synth.rooms_map(400, seed=3)
     pose = synth.room_centre_pose(400, 0.05)
@@ -301,6 +303,12 @@ def test_resample_bit_exact_vs_oracle(lib, port, kind, n, seed):
     else:
         cloud = synth.uniform_cloud(occ, 0.05, n, seed)
     w = np.random.default_rng(seed).gamma(0.7, size=n)
+    if kind == "spiky":
+        # two samples hold 80 % of the weight, a long run holds none at all:
+        # buckets that span one entry, buckets that span tens of thousands
+        w[n // 3] = 2.0 * w.sum()
+        w[n // 2] = 0.5 * w.sum()
+        w[n // 2 + 1:n // 2 + 30000] = 0.0
     cloud[:, 3] = w / w.sum()
     cnt, k, ncl = _check_resample_against_oracle(lib, port, occ, cloud, 100, 0.01, 0.99, 50 + seed)
     if kind == "tracking" and n == 20000:
