@@ -132,8 +132,11 @@ __device__ PairFn block_scan_fn(PairFn v, PairFn *total, PairFn *s_warp)
 }
 
 // ---- A: fp64 sum of each tile (any fixed order; only used for classification)
+// When the weights sit inside 32-byte particle records (stride 4) this pass also
+// writes them out contiguously: the four later passes then read 8 B per weight
+// instead of dragging the whole record through the memory system each time.
 __global__ void cs_tile_sums(const Weights W, int n, double *__restrict__ tile_sum,
-                             double *__restrict__ tile_max)
+                             double *__restrict__ tile_max, double *__restrict__ packed)
 {
   __shared__ double s_red[32];
   const int base = blockIdx.x * kTileLen;
@@ -145,6 +148,7 @@ __global__ void cs_tile_sums(const Weights W, int n, double *__restrict__ tile_s
     if (i < n)
     {
       const double w = W[i];
+      if (packed) packed[i] = w;
       v += w;
       mx = fmax(mx, w);
     }
@@ -420,8 +424,19 @@ void exact_cumsum_parallel(PfCtx *c, Weights W, int n, double *d_cum)
     AMCL_CUDA(cudaMalloc(&c->d_tile_class, sizeof(int) * (size_t)c->tile_cap));
   }
   PairFn *tile_fn = reinterpret_cast<PairFn *>(c->d_tile_fn);
-  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_carry);
+  double *packed = nullptr;
+  if (W.stride != 1)
+  {
+    if (!c->d_wpack) AMCL_CUDA(cudaMalloc(&c->d_wpack, sizeof(double) * (size_t)c->alloc_samples));
+    packed = c->d_wpack;
+  }
+  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_carry, packed);
   AMCL_LAUNCH_CHECK();
+  if (packed)
+  {
+    W.p = packed;
+    W.stride = 1;
+  }
   const int bad_slot = 8, dirty_slot = 9;
   AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, 2 * sizeof(int), st));
   cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, c->d_tile_carry, tiles, n, c->d_tile_class,

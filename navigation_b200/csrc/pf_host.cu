@@ -175,7 +175,7 @@ void pf_enable_peers(PfCtx *c)
     AMCL_CUDA(cudaMemcpy((void *)c->d_peer_tab[j], tab.data(), sizeof(Particle *) * (size_t)sh.world,
                          cudaMemcpyHostToDevice));
   }
-  AMCL_CUDA(cudaMalloc(&c->d_wpack, sizeof(double) * (size_t)c->alloc_samples));
+  if (!c->d_wpack) AMCL_CUDA(cudaMalloc(&c->d_wpack, sizeof(double) * (size_t)c->alloc_samples));
   c->peers_ready = true;
 }
 
