@@ -346,12 +346,15 @@ struct PickArgs
   int first;                // first candidate index handled by this launch
   int count;                // number of candidates handled
   int write_keys;           // 0: poses only (re-pick after the cut)
+  double weight;            // written to every picked sample
   double bin_x, bin_y, bin_t;
 };
 
 // One thread per candidate sample m: binary search of r_m in the cumulative
-// table, pose copy, bin key.  The weight is written as 1.0 (pf.c:475) and
-// rescaled once n is known.
+// table, pose copy, bin key.  The reference writes weight 1.0 (pf.c:475) and
+// rescales to 1/n once n is known (pf.c:493-498); here the weight written is
+// 1/max_samples, final whenever the KLD bound does not cut the set (only a cut
+// set is rewritten).
 __global__ void pick_and_copy(const PickArgs a)
 {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -379,7 +382,7 @@ __global__ void pick_and_copy(const PickArgs a)
     const Particle *base = a.peers ? a.peers[lo / a.peer_chunk] : a.src;
     s = load_particle(base + lo);
   }
-  s.w = 1.0;
+  s.w = a.weight;
   store_particle(a.dst + m, s);
   a.src_index[m] = from;
   if (a.write_keys) a.keys[m] = pose_key(s, a.bin_x, a.bin_y, a.bin_t);
@@ -1563,6 +1566,7 @@ void run_resample(PfCtx *c)
   pa.src_index = c->d_src;
   pa.keys = c->d_keys;
   pa.write_keys = 1;
+  pa.weight = 1.0 / (double)maxs;
   // a sharded rank picks only its slice of the candidate samples ...
   pa.first = sh.lo(maxs);
   pa.count = sh.count(maxs);
@@ -1715,6 +1719,7 @@ void run_resample(PfCtx *c)
     pa.first = own_lo;
     pa.count = own_cnt;
     pa.write_keys = 0;
+    pa.weight = 1.0 / (double)n;
     pick_and_copy<<<blocks_for(own_cnt, 256), 256, 0, st>>>(pa);
     AMCL_LAUNCH_CHECK();
     if (shared_grid)
@@ -1726,8 +1731,8 @@ void run_resample(PfCtx *c)
       AMCL_LAUNCH_CHECK();
     }
   }
-  // pf.c:493-498: every weight is 1/n
-  if (own_cnt > 0)
+  // pf.c:493-498: every weight is 1/n (already so unless the set was cut on one GPU)
+  if (own_cnt > 0 && n != maxs && !sh.on())
   {
     set_uniform_weight<<<blocks_for(own_cnt, 256), 256, 0, st>>>(c->d_set[ib] + own_lo, own_cnt,
                                                                  1.0 / (double)n);
