@@ -174,6 +174,7 @@ struct PfCtx
   double *d_scan_tab = nullptr;
   int scan_tab_cap = 0;
   double *d_skip = nullptr;       // beam-skip pass: per-beam agreement counts + code->agree bytes
+  unsigned int *d_rootlist = nullptr;  // cluster roots + their earliest samples (short-list ranking)
   int *d_bucket_index = nullptr;  // bucket index of the cumulative table (resample_dev.cu)
   size_t bucket_cap = 0;
   double *d_cloud = nullptr;      // packed PoseArray for the caller (amclb200_pf_pack_cloud)

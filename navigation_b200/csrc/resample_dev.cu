@@ -814,6 +814,62 @@ __global__ void cc_jump(const BinTable T, unsigned int nslots, int n_valid, int 
   }
 }
 
+// Every bin follows its parents to the root and points at it directly.  Other
+// threads only ever overwrite a parent pointer with that bin's root, so a chain
+// read while it is being shortened still ends at the same root.
+__global__ void cc_flatten(const BinTable T, unsigned int nslots, int n_valid)
+{
+  const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  unsigned int p = __ldcg(&T.aux[s]);
+  for (;;)
+  {
+    const unsigned int gp = __ldcg(&T.aux[p]);
+    if (gp == p) break;
+    p = gp;
+  }
+  T.aux[s] = p;
+}
+
+// Few clusters (the usual case): the roots are collected in a short list and
+// ranked by their earliest sample directly, instead of flagging and scanning
+// all n sample indices.
+constexpr int kRootListCap = 4096;
+
+__global__ void cc_collect_roots(const BinTable T, unsigned int nslots, int n_valid,
+                                 const unsigned int *__restrict__ cmin, unsigned int *list,
+                                 unsigned int *keys, int *count)
+{
+  const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (T.aux[s] != s) return;
+  const int k = atomicAdd(count, 1);
+  if (k < kRootListCap)
+  {
+    list[k] = s;
+    keys[k] = cmin[s];
+  }
+}
+
+// id of a root = number of roots whose earliest sample comes before its own
+__global__ void cc_rank_roots(const unsigned int *__restrict__ list, const unsigned int *__restrict__ keys,
+                              int count, unsigned int *cmin_to_id)
+{
+  __shared__ unsigned int s_keys[256];
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned int mine = t < count ? keys[t] : 0u;
+  unsigned int rank = 0;
+  for (int base = 0; base < count; base += 256)
+  {
+    __syncthreads();
+    if (base + (int)threadIdx.x < count) s_keys[threadIdx.x] = keys[base + threadIdx.x];
+    __syncthreads();
+    const int m = min(256, count - base);
+    for (int k = 0; k < m; k++) rank += s_keys[k] < mine;
+  }
+  if (t < count) cmin_to_id[list[t]] = rank;
+}
+
 // smallest first-sample index of every component, kept at its root
 __global__ void cc_component_min(const BinTable T, unsigned int nslots, int n_valid,
                                  unsigned int *cmin)
@@ -823,9 +879,16 @@ __global__ void cc_component_min(const BinTable T, unsigned int nslots, int n_va
   const unsigned int f = T.first[s];
   if (f >= (unsigned int)n_valid) return;
   // A giant component would otherwise serialise millions of atomics on one
-  // address: look first, and only compete when this bin can lower the value.
-  unsigned int *slot = &cmin[T.aux[s]];
-  if (f < __ldcg(slot)) atomicMin(slot, f);
+  // address: lanes of a warp that share a root combine first, and the group's
+  // leader looks before it competes.
+  const unsigned int root = T.aux[s];
+  const unsigned int peers = __match_any_sync(__activemask(), root);
+  const unsigned int best = __reduce_min_sync(peers, f);
+  if ((int)(threadIdx.x & 31) == __ffs(peers) - 1)
+  {
+    unsigned int *slot = &cmin[root];
+    if (best < __ldcg(slot)) atomicMin(slot, best);
+  }
 }
 
 // Canonical cluster numbers: clusters are numbered in the order in which their
@@ -1202,32 +1265,41 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
     cc_link<<<sb, 256, 0, st>>>(T, nslots, n);
     AMCL_LAUNCH_CHECK();
   }
-  // flatten: rounds of pointer jumping in groups of four, until a round moves nothing
-  for (int group = 0; group < 16; group++)
-  {
-    AMCL_CUDA(cudaMemsetAsync(c->d_ints + I_MOVED, 0, sizeof(int), st));
-    for (int r = 0; r < 4; r++)
-    {
-      if (r == 3) AMCL_CUDA(cudaMemsetAsync(c->d_ints + I_MOVED, 0, sizeof(int), st));
-      cc_jump<<<sb, 256, 0, st>>>(T, nslots, n, c->d_ints + I_MOVED);
-      AMCL_LAUNCH_CHECK();
-    }
-    sync_ints(c, I_MOVED, 1);
-    if (!c->h_ints[I_MOVED]) break;
-  }
+  cc_flatten<<<sb, 256, 0, st>>>(T, nslots, n);
+  AMCL_LAUNCH_CHECK();
   cc_component_min<<<sb, 256, 0, st>>>(T, nslots, n, cmin);
   AMCL_LAUNCH_CHECK();
-  // cluster-opening flags reuse d_keys' storage as u32 scratch (keys are spent)
-  unsigned int *cflag = reinterpret_cast<unsigned int *>(c->d_keys);
-  unsigned int *cscan = cflag + c->alloc_samples;
-  AMCL_CUDA(cudaMemsetAsync(cflag, 0, sizeof(unsigned int) * (size_t)(n > 0 ? n : 1), st));
-  cc_flag_roots<<<sb, 256, 0, st>>>(T, nslots, n, cmin, cflag);
-  AMCL_LAUNCH_CHECK();
-  scan_u32(c, cflag, cscan, n, I_CLUSTERS);
-  cc_assign_ids<<<sb, 256, 0, st>>>(T, nslots, n, cscan, cmin);
+  // canonical ids: short root list when there are few clusters ...
+  if (!c->d_rootlist) AMCL_CUDA(cudaMalloc(&c->d_rootlist, sizeof(unsigned int) * 2 * kRootListCap));
+  AMCL_CUDA(cudaMemsetAsync(c->d_ints + I_CLUSTERS, 0, sizeof(int), st));
+  cc_collect_roots<<<sb, 256, 0, st>>>(T, nslots, n, cmin, c->d_rootlist, c->d_rootlist + kRootListCap,
+                                       c->d_ints + I_CLUSTERS);
   AMCL_LAUNCH_CHECK();
   sync_ints(c, I_CLUSTERS, 1);
-  const int ncl = c->h_ints[I_CLUSTERS];
+  int ncl = c->h_ints[I_CLUSTERS];
+  if (ncl <= kRootListCap)
+  {
+    if (ncl > 0)
+    {
+      cc_rank_roots<<<blocks_for(ncl, 256), 256, 0, st>>>(c->d_rootlist, c->d_rootlist + kRootListCap, ncl, cmin);
+      AMCL_LAUNCH_CHECK();
+    }
+  }
+  else
+  {
+    // ... otherwise flag every cluster's earliest sample and scan the flags.
+    // The flags reuse d_keys' storage as u32 scratch (keys are spent).
+    unsigned int *cflag = reinterpret_cast<unsigned int *>(c->d_keys);
+    unsigned int *cscan = cflag + c->alloc_samples;
+    AMCL_CUDA(cudaMemsetAsync(cflag, 0, sizeof(unsigned int) * (size_t)(n > 0 ? n : 1), st));
+    cc_flag_roots<<<sb, 256, 0, st>>>(T, nslots, n, cmin, cflag);
+    AMCL_LAUNCH_CHECK();
+    scan_u32(c, cflag, cscan, n, I_CLUSTERS);
+    cc_assign_ids<<<sb, 256, 0, st>>>(T, nslots, n, cscan, cmin);
+    AMCL_LAUNCH_CHECK();
+    sync_ints(c, I_CLUSTERS, 1);
+    ncl = c->h_ints[I_CLUSTERS];
+  }
 
   if (ncl > c->cluster_acc_cap)
   {
