@@ -360,6 +360,14 @@ def b200_arm(args):
         "peak_source": "measured live: uncorrelated 2-byte gathers over a %d MB table (one 32-B sector each)" % (map_bytes >> 20),
         "hbm_peak_gbs": hbm, "hbm_peak_source": "MEASURED_PEAKS.json" if os.path.exists(peaks_file) else "fallback",
     }
+    # The bound that actually binds (ablations): instruction issue.  One evaluation is 20 SASS
+    # instructions per warp of which 7 are fp64 (two dispatch cycles each): 27 issue cycles.
+    props = torch.cuda.get_device_properties(local)
+    sm_hz = 1e6 * ((clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0)
+    issue_peak = props.multi_processor_count * 4 * sm_hz * 32 / 27.0
+    roofline["issue"] = {"issue_cycles_per_warp_eval": 27, "peak_evals_per_s": issue_peak,
+                         "frac": roofline["evals_per_s"] / issue_peak,
+                         "note": "4 schedulers x SMs x SM clock x 32 lanes / 27 cycles; SASS count from cuobjdump"}
 
     # ---- e2e: host buffers through the reference-facing API ------------------
     # The step() above already IS the reference-facing call sequence with the

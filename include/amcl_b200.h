@@ -135,6 +135,15 @@ void amclb200_pf_load_device(pf_t *pf, const void *d_particles, int n);
  * mean and covariance of the heaviest cluster of the current set; -1 if none. */
 int amclb200_pf_best_cluster(pf_t *pf, double *weight, pf_vector_t *mean, pf_matrix_t *cov);
 
+/* Host mirror of the map.  eager (default 1): map_update_cspace re-reads
+ * cells[].occ_state and writes cells[].occ_dist on every call, as the reference
+ * does.  eager 0: the device copy is authoritative -- the cells are read once
+ * (not at all for a map made by amclb200_map_from_image) and cells[].occ_dist
+ * is written only by amclb200_map_pull_distances.  The laser models never read
+ * the host cells either way. */
+void amclb200_map_set_mirror(map_t *map, int eager);
+void amclb200_map_pull_distances(map_t *map);
+
 /* ---- the data formats either side of the filter (N2, N4) -----------
  *
  * Map ingest: map_server's image -> occupancy rule

@@ -61,6 +61,7 @@ struct MapCtx
   double max_occ_dist = 0;
   bool occ_uploaded = false;
   bool dist_valid = false;
+  bool mirror_eager = true;       // map_update_cspace re-reads cells[].occ_state and writes cells[].occ_dist
   uint64_t generation = 0;        // bumps whenever codes / R / scale change
 
   int8_t *d_occ = nullptr;        // [sy][sx] occupancy states

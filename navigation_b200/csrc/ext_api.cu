@@ -37,6 +37,15 @@ void *amclb200_pf_device_samples(pf_t *pf, int set_index)
   return pf_ctx(pf)->d_set[set_index & 1];
 }
 
+void amclb200_map_set_mirror(map_t *map, int eager) { map_ctx(map, true)->mirror_eager = eager != 0; }
+
+void amclb200_map_pull_distances(map_t *map)
+{
+  MapCtx *m = map_ctx(map, true);
+  if (!m->dist_valid) AMCL_FATAL("amclb200_map_pull_distances: no distance map has been computed");
+  map_codes_to_host_cells(m);
+}
+
 void amclb200_map_push_distances(map_t *map)
 {
   MapCtx *m = map_ctx(map, true);

@@ -576,9 +576,15 @@ int map_load_occ(map_t *map, const char *filename, double scale, int negate)
 void map_update_cspace(map_t *map, double max_occ_dist)
 {
   MapCtx *m = map_ctx(map, true);
-  map_upload_occupancy(m);
+  // amclb200_map_set_mirror(map, 0): the device copy is authoritative -- the
+  // caller's cells are read once (or never, after amclb200_map_from_image) and
+  // cells[].occ_dist is filled only by amclb200_map_pull_distances
+  if (m->mirror_eager || !m->occ_uploaded) map_upload_occupancy(m);
   map_build_distance_codes(m, max_occ_dist);
-  map_codes_to_host_cells(m);
+  if (m->mirror_eager)
+    map_codes_to_host_cells(m);
+  else
+    map->max_occ_dist = max_occ_dist;
 }
 
 // map_range.c:38-120.  A single ray is a host call in the reference API (the

@@ -55,6 +55,8 @@ EXTENSION_SYMBOLS = {
     "amclb200_pf_pack_cloud": (C.c_int, [abi.pf_p, C.c_int, C.c_int, C.c_void_p]),
     "amclb200_inflate_costs": (C.c_int, [C.c_void_p] + [C.c_int] * 7 + [C.c_double] * 4 + [C.c_int]),
     "amclb200_inflate_last_ms": (C.c_float, []),
+    "amclb200_map_set_mirror": (None, [abi.map_p, C.c_int]),
+    "amclb200_map_pull_distances": (None, [abi.map_p]),
 }
 
 RNG_PHILOX, RNG_DRAND48 = 0, 1

@@ -87,6 +87,9 @@ def edt_case(size):
     side = Side(lib, occ)
     t_api = timed(lambda: side.update_cspace(2.0), reps=3, warm=1)     # upload + kernels + host cells
     t_dev = lib.amclb200_map_last_edt_ms(side.map)
+    lib.amclb200_map_set_mirror(side.map, 0)                            # device-authoritative map
+    t_api_dev = timed(lambda: side.update_cspace(2.0), reps=5, warm=1)
+    lib.amclb200_map_set_mirror(side.map, 1)
     d_occ = torch.from_numpy(occ).cuda()
     codes = torch.empty((size, size), dtype=torch.int16, device="cuda")
     ok = size * size <= lib.amclb200_edt_static_max_cells()
@@ -102,7 +105,8 @@ def edt_case(size):
         torch.cuda.synchronize()
         t_k = e0.elapsed_time(e1) / 10
     side.close()
-    return dict(config="K3 map_update_cspace", map=size, api_ms=t_api, edt_kernels_ms=t_dev,
+    return dict(config="K3 map_update_cspace", map=size, api_ms=t_api, api_ms_device_authoritative=t_api_dev,
+                edt_kernels_ms=t_dev,
                 edt_hbm_frac=3 * size * size / (t_dev * 1e-3) / 1e9 / HBM, kernels_ms_static_variant=t_k,
                 algorithmic_bytes=3 * size * size,
                 hbm_frac=(3 * size * size / (t_k * 1e-3) / 1e9 / HBM) if t_k else None)

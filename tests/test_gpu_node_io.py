@@ -106,6 +106,27 @@ def test_ingested_map_drives_the_filter_like_an_uploaded_one(gpu_lib):
     lib.map_free(m)
 
 
+def test_device_authoritative_map(gpu_lib):
+    """amclb200_map_set_mirror(map, 0): map_update_cspace neither re-reads the host
+    cells nor writes occ_dist; amclb200_map_pull_distances fills them on demand."""
+    lib = gpu_lib
+    occ = synth.rooms_map(300, seed=8)
+    img = np.where(occ == 1, 0, np.where(occ == -1, 254, 205)).astype(np.uint8)[::-1]
+    m, _ = ingest(lib, img, False, 0.65, 0.196, "trinary", res=0.05)
+    lib.amclb200_map_set_mirror(m, 0)
+    lib.map_update_cspace(m, 1.5)
+    got = np.empty((300, 300))
+    lib.amcl_c_map_get_occ_dist(m, got.ctypes.data)
+    assert np.all(got == 0.0) and m.contents.max_occ_dist == 1.5
+    lib.amclb200_map_pull_distances(m)
+    lib.amcl_c_map_get_occ_dist(m, got.ctypes.data)
+    side = Side(lib, occ)
+    side.update_cspace(1.5)
+    assert np.array_equal(got, side.occ_dist())
+    side.close()
+    lib.map_free(m)
+
+
 @pytest.mark.parametrize("n,stride", [(1000, 1), (100003, 7), (5, 10)])
 def test_pack_cloud_vs_oracle(gpu_lib, n, stride):
     lib = gpu_lib
