@@ -272,8 +272,26 @@ struct BeamArgs
   double *block_totals;
 };
 
+// floor(t / d) for 0 <= t < 2^24, 0 < d, with d's reciprocal at hand: the float
+// product is within 1e-6 of the quotient, one correction step makes it exact.
+__device__ __forceinline__ int floor_div_small(int t, int d, float inv_d)
+{
+  int q = (int)((float)t * inv_d);
+  if ((q + 1) * d <= t) q++;
+  else if (q * d > t) q--;
+  return q;
+}
+
 // map_calc_range (map_range.c:38-120) on the bit-tiled occupancy: returns the
 // range in metres.  The current 8x8 tile word is cached in a register.
+//
+// The reference steps one cell at a time.  The error term of its line stepping
+// has a closed form: with the invariant -dx <= 2 err < dx, after k more steps the
+// minor coordinate has advanced m(k) = floor((2 (err + k dy) + dx) / (2 dx)) times
+// and err has become err + k dy - m(k) dx.  When the tile under the ray is
+// entirely free (word == 0; cells outside the map count as blocked in edge
+// tiles) the walk therefore jumps straight to the first cell outside the tile --
+// the same cells are visited afterwards, in the same state.
 __device__ __forceinline__ double cast_ray(const BeamArgs &a, int x0, int y0, int x1, int y1)
 {
   const bool steep = abs(y1 - y0) > abs(x1 - x0);
@@ -287,6 +305,9 @@ __device__ __forceinline__ double cast_ray(const BeamArgs &a, int x0, int y0, in
   int x = x0, y = y0, err = 0;
   int cur_tile = -1;
   uint64_t word = 0;
+  const bool can_jump = dx > 0 && dx < (1 << 18);      // keeps every intermediate below 2^24
+  const float inv_2dx = can_jump ? 1.0f / (float)(2 * dx) : 0.0f;
+  const float inv_2dy = (can_jump && dy > 0) ? 1.0f / (float)(2 * dy) : 0.0f;
   for (;;)
   {
     const int ci = steep ? y : x, cj = steep ? x : y;
@@ -298,6 +319,23 @@ __device__ __forceinline__ double cast_ray(const BeamArgs &a, int x0, int y0, in
       {
         cur_tile = tile;
         word = __ldg(a.blocked + tile);
+      }
+      if (word == 0ull && can_jump)
+      {
+        const int rem = (x1 + xs - x) * xs;                       // steps until the walk's own end
+        int k = xs > 0 ? 8 - (x & 7) : (x & 7) + 1;               // steps until x leaves the tile
+        if (dy > 0)
+        {
+          const int my = ys > 0 ? 8 - (y & 7) : (y & 7) + 1;      // minor advances until y leaves it
+          const int num = my * 2 * dx - dx - 2 * err;             // smallest k with m(k) >= my: ceil(num / 2dy)
+          k = min(k, floor_div_small(num + 2 * dy - 1, 2 * dy, inv_2dy));
+        }
+        if (k > rem) return a.range_max;                           // the walk ends inside the free tile
+        const int m = floor_div_small(2 * (err + k * dy) + dx, 2 * dx, inv_2dx);
+        x += k * xs;
+        y += m * ys;
+        err += k * dy - m * dx;
+        continue;
       }
       stop = (word >> (((cj & 7) << 3) | (ci & 7))) & 1ull;
     }
