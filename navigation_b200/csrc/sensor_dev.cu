@@ -130,17 +130,25 @@ likelihood_field_kernel(const LfArgs a)
   int *s_counts = nullptr;
 
   const uint32_t beam_bytes = (uint32_t)a.nb_pad * (uint32_t)sizeof(double2);
-  const uint32_t lut_bytes = LUT_IN_SMEM ? (uint32_t)a.ncodes_pad * 8u : 0u;
+  const uint32_t lut_bytes = (LUT_IN_SMEM && MODE != MODE_COUNT) ? (uint32_t)a.ncodes_pad * 8u : 0u;
   bulk_stage_begin(&s_bar, beam_bytes + lut_bytes);
   if (threadIdx.x == 0)
   {
     bulk_stage_copy(s_beams, a.beams, beam_bytes, &s_bar);
-    if (LUT_IN_SMEM) bulk_stage_copy(s_lut, a.lut, lut_bytes, &s_bar);
+    if (LUT_IN_SMEM && MODE != MODE_COUNT) bulk_stage_copy(s_lut, a.lut, lut_bytes, &s_bar);
   }
+  unsigned char *s_agree = nullptr;
   if (MODE == MODE_COUNT)
   {
-    s_counts = reinterpret_cast<int *>(smem_raw + (size_t)a.nb_pad * sizeof(double2) + lut_bytes);
-    for (int k = threadIdx.x; k < a.nb; k += blockDim.x) s_counts[k] = 0;
+    // COUNT mode keeps no likelihood table; after the beams come one private
+    // row of per-beam counters per warp (beam i is only ever touched by lane
+    // i % 32 of that warp: plain read-modify-write, no atomics) and the
+    // code -> "agrees" bytes.
+    s_counts = reinterpret_cast<int *>(smem_raw + (size_t)a.nb_pad * sizeof(double2));
+    const int rows = blockDim.x >> 5;
+    for (int k = threadIdx.x; k < rows * a.nb; k += blockDim.x) s_counts[k] = 0;
+    s_agree = reinterpret_cast<unsigned char *>(s_counts + rows * a.nb);
+    for (int k = threadIdx.x; k < a.ncodes_pad; k += blockDim.x) s_agree[k] = a.agree[k];
   }
   __syncthreads();  // barrier init visible to all before anyone polls it
   bulk_stage_wait(&s_bar);
@@ -201,15 +209,18 @@ likelihood_field_kernel(const LfArgs a)
         const unsigned mj = min((unsigned)floor_to_int(fma(ps[q], b.x, fma(pc[q], b.y, pY[q]))), usy);
         c[q] = __ldg(code + cell_index(mi, mj, k_row));
       }
-#pragma unroll
-      for (int q = 0; q < kBlockP; q++)
+      if (MODE == MODE_COUNT)
       {
-        if (MODE == MODE_COUNT)
-        {
-          if (p0 + q < a.n && a.agree[c[q]]) atomicAdd(&s_counts[i], 1);
-        }
-        else
-          acc[q] += lut[c[q]];
+        int agreeing = 0;
+#pragma unroll
+        for (int q = 0; q < kBlockP; q++)
+          if (p0 + q < a.n) agreeing += s_agree[c[q]];
+        s_counts[(threadIdx.x >> 5) * a.nb + i] += agreeing;
+      }
+      else
+      {
+#pragma unroll
+        for (int q = 0; q < kBlockP; q++) acc[q] += lut[c[q]];
       }
     }
     if (MODE != MODE_COUNT)
@@ -234,8 +245,13 @@ likelihood_field_kernel(const LfArgs a)
   if (MODE == MODE_COUNT)
   {
     __syncthreads();
+    const int rows = blockDim.x >> 5;
     for (int k = threadIdx.x; k < a.nb; k += blockDim.x)
-      if (s_counts[k]) atomicAdd(&a.beam_counts[k], s_counts[k]);
+    {
+      int total = 0;
+      for (int r = 0; r < rows; r++) total += s_counts[r * a.nb + k];
+      if (total) atomicAdd(&a.beam_counts[k], total);
+    }
   }
   else
   {
@@ -575,8 +591,14 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
 
   const size_t beam_bytes = (size_t)a.nb_pad * sizeof(double2);
   const size_t lut_bytes = (size_t)ncodes_pad * 8;
-  const bool lut_smem = beam_bytes + lut_bytes + (count_mode ? sizeof(int) * (size_t)nb : 0) <= 96 * 1024;
-  const size_t smem = beam_bytes + (lut_smem ? lut_bytes : 0) + (count_mode ? sizeof(int) * (size_t)(nb + 1) : 0);
+  const size_t count_bytes =
+      count_mode ? sizeof(int) * (size_t)(kSensorThreads / 32) * (size_t)nb + (size_t)ncodes_pad + 16 : 0;
+  const bool lut_smem = count_mode ? beam_bytes + count_bytes <= 200 * 1024
+                                   : beam_bytes + lut_bytes <= 96 * 1024;
+  if (count_mode && !lut_smem)
+    AMCL_FATAL("beam skipping with %d beams needs %zu bytes of shared memory per block", nb,
+               beam_bytes + count_bytes);
+  const size_t smem = count_mode ? beam_bytes + count_bytes : beam_bytes + (lut_smem ? lut_bytes : 0);
 
   int grid;
   if (!c->ev_a)
