@@ -799,21 +799,6 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid)
   }
 }
 
-// One round of pointer jumping: every bin adopts its grandparent.  Repeated
-// until nothing moves (depth halves per round), every bin points at its root.
-__global__ void cc_jump(const BinTable T, unsigned int nslots, int n_valid, int *moved)
-{
-  const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
-  const unsigned int p = __ldcg(&T.aux[s]);
-  const unsigned int gp = __ldcg(&T.aux[p]);
-  if (gp != p)
-  {
-    T.aux[s] = gp;
-    *moved = 1;
-  }
-}
-
 // Every bin follows its parents to the root and points at it directly.  Other
 // threads only ever overwrite a parent pointer with that bin's root, so a chain
 // read while it is being shortened still ends at the same root.
