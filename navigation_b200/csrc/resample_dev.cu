@@ -703,16 +703,17 @@ __device__ __forceinline__ void suf_union(unsigned int *lab, unsigned int a, uns
 }
 
 __global__ void __launch_bounds__(kBrickCells)
-cc_brick_local(const BinTable T, int bricks_x, int bricks_y, int n_valid, unsigned int *cmin)
+cc_brick_local(const BinTable T, int bricks_x, int bricks_y, int n_valid, unsigned int *cmin, int brick_base)
 {
+  const int brick = (int)blockIdx.x + brick_base;
   __shared__ unsigned int s_lab[kBrickCells];
   __shared__ unsigned char s_occ[kBrickCells];
   const int lx = threadIdx.x & (kBrickX - 1);
   const int ly = (threadIdx.x / kBrickX) & (kBrickY - 1);
   const int lt = threadIdx.x / (kBrickX * kBrickY);
-  const int bx = blockIdx.x % bricks_x;
-  const int by = (blockIdx.x / bricks_x) % bricks_y;
-  const int bt = blockIdx.x / (bricks_x * bricks_y);
+  const int bx = brick % bricks_x;
+  const int by = (brick / bricks_x) % bricks_y;
+  const int bt = brick / (bricks_x * bricks_y);
   const int ix = bx * kBrickX + lx, iy = by * kBrickY + ly, it = bt * kBrickT + lt;
   const bool inside = ix < T.ex && iy < T.ey && it < T.et;
   const unsigned int s = inside ? (unsigned int)((it * T.ey + iy) * T.ex + ix) : 0u;
@@ -760,14 +761,20 @@ cc_brick_local(const BinTable T, int bricks_x, int bricks_y, int n_valid, unsign
 }
 
 __global__ void __launch_bounds__(kBrickCells)
-cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid)
+cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int brick_base,
+                 int bricks_per_owner, int phase)
 {
+  // Sharded labelling splits the bricks into contiguous runs, one per rank
+  // (bricks_per_owner > 0).  Phase 1 (own bricks only): pairs whose two bricks
+  // have the same owner.  Phase 2 (all bricks, after the ranks' forests have been
+  // merged): the pairs that straddle owners.  Unsharded: one pass, every pair.
+  const int brick = (int)blockIdx.x + brick_base;
   const int lx = threadIdx.x & (kBrickX - 1);
   const int ly = (threadIdx.x / kBrickX) & (kBrickY - 1);
   const int lt = threadIdx.x / (kBrickX * kBrickY);
-  const int bx = blockIdx.x % bricks_x;
-  const int by = (blockIdx.x / bricks_x) % bricks_y;
-  const int bt = blockIdx.x / (bricks_x * bricks_y);
+  const int bx = brick % bricks_x;
+  const int by = (brick / bricks_x) % bricks_y;
+  const int bt = brick / (bricks_x * bricks_y);
   const int ix = bx * kBrickX + lx, iy = by * kBrickY + ly, it = bt * kBrickT + lt;
   if (ix >= T.ex || iy >= T.ey || it >= T.et) return;
   // only cells on a forward face (or next to the low-x / low-y face, whose
@@ -785,6 +792,12 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid)
     const int nx = ix + dx, ny = iy + dy, nt = it + dt;
     if ((unsigned)nx >= (unsigned)T.ex || (unsigned)ny >= (unsigned)T.ey || (unsigned)nt >= (unsigned)T.et)
       continue;
+    if (bricks_per_owner > 0)
+    {
+      const int nbrick = ((nt / kBrickT) * bricks_y + ny / kBrickY) * bricks_x + nx / kBrickX;
+      const bool same_owner = nbrick / bricks_per_owner == brick / bricks_per_owner;
+      if (same_owner != (phase == 1)) continue;
+    }
     const unsigned int nb = (unsigned int)((nt * T.ey + ny) * T.ex + nx);
     if (T.first[nb] >= (unsigned int)n_valid) continue;
     // same pruning as in cc_brick_local, now with any cell of the grid in between
@@ -1238,10 +1251,36 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
     const int bxn = (T.ex + kBrickX - 1) / kBrickX, byn = (T.ey + kBrickY - 1) / kBrickY,
               btn = (T.et + kBrickT - 1) / kBrickT;
     const int bricks = bxn * byn * btn;
-    cc_brick_local<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, cmin);
-    AMCL_LAUNCH_CHECK();
-    cc_brick_borders<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n);
-    AMCL_LAUNCH_CHECK();
+    const Shard &sh = c->shard;
+    if (sh.on() && bricks >= 64 * sh.world)
+    {
+      // Every rank labels a contiguous run of bricks; the forests (disjoint sets
+      // of cells, everything else 0xFFFFFFFF = -1) are merged with one MAX
+      // all-reduce; the links between runs are then added by everybody.  Roots
+      // are always the smallest cell index of their tree, so all ranks end up
+      // with identical forests.
+      const int per = (bricks + sh.world - 1) / sh.world;
+      const int b_lo = min(sh.rank * per, bricks), b_hi = min(b_lo + per, bricks);
+      AMCL_CUDA(cudaMemsetAsync(T.aux, 0xFF, sizeof(unsigned int) * (size_t)nslots, st));
+      AMCL_CUDA(cudaMemsetAsync(cmin, 0xFF, sizeof(unsigned int) * (size_t)nslots, st));
+      if (b_hi > b_lo)
+      {
+        cc_brick_local<<<b_hi - b_lo, kBrickCells, 0, st>>>(T, bxn, byn, n, cmin, b_lo);
+        AMCL_LAUNCH_CHECK();
+        cc_brick_borders<<<b_hi - b_lo, kBrickCells, 0, st>>>(T, bxn, byn, n, b_lo, per, 1);
+        AMCL_LAUNCH_CHECK();
+      }
+      sh.allreduce(T.aux, (int)nslots, SHARD_I32, SHARD_MAX, sh.user);
+      cc_brick_borders<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, 0, per, 2);
+      AMCL_LAUNCH_CHECK();
+    }
+    else
+    {
+      cc_brick_local<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, cmin, 0);
+      AMCL_LAUNCH_CHECK();
+      cc_brick_borders<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, 0, 0, 0);
+      AMCL_LAUNCH_CHECK();
+    }
   }
   else
   {
