@@ -224,14 +224,10 @@ __global__ void edt_pack_rows(const int8_t *__restrict__ occ, int sx, int sy, in
   if (lane == 0) bits[(size_t)j * stride + (w + pad)] = word;
 }
 
-__global__ void edt_row_bits(const unsigned long long *__restrict__ bits, int sx, int sy, int words,
-                             int pad, int R, unsigned char *__restrict__ g)
+// distance along the row from cell i to the nearest set bit of A (bit strings
+// with `pad` zero words on both sides), capped at R + 1
+__device__ __forceinline__ int row_distance(const unsigned long long *__restrict__ A, int i, int R)
 {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = blockIdx.y;
-  if (i >= sx) return;
-  const int stride = words + 2 * pad;
-  const unsigned long long *A = bits + (size_t)j * stride + pad;   // A[-pad .. words+pad)
   const int k = i >> 6, sft = i & 63;
   // towards lower x: bits i, i-1, ... ; towards higher x: bits i, i+1, ...
   int left = R + 1, right = R + 1;
@@ -266,8 +262,32 @@ __global__ void edt_row_bits(const unsigned long long *__restrict__ bits, int sx
     }
   }
   int best = left < right ? left : right;
-  if (best > R + 1) best = R + 1;
-  g[(size_t)j * sx + i] = (unsigned char)best;
+  return best > R + 1 ? R + 1 : best;
+}
+
+// One thread per four neighbouring cells (one 4-byte store) when the row pitch
+// allows it, else per cell.
+__global__ void edt_row_bits(const unsigned long long *__restrict__ bits, int sx, int sy, int words,
+                             int pad, int R, unsigned char *__restrict__ g)
+{
+  const int j = blockIdx.y;
+  const int stride = words + 2 * pad;
+  const unsigned long long *A = bits + (size_t)j * stride + pad;   // A[-pad .. words+pad)
+  if ((sx & 3) == 0)
+  {
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i >= sx) return;
+    unsigned v = 0;
+#pragma unroll
+    for (int b = 0; b < 4; b++) v |= (unsigned)row_distance(A, i + b, R) << (8 * b);
+    *reinterpret_cast<unsigned *>(g + (size_t)j * sx + i) = v;
+    return;
+  }
+  for (int b = 0; b < 4; b++)
+  {
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4 + b;
+    if (i < sx) g[(size_t)j * sx + i] = (unsigned char)row_distance(A, i, R);
+  }
 }
 
 constexpr int kPatchX = 64, kPatchY = 32;
@@ -282,11 +302,27 @@ edt_col_pass(const unsigned char *__restrict__ g, int sx, int sy, int R, int til
   uint16_t *s_out = reinterpret_cast<uint16_t *>(s_raw + (((size_t)rows * kPatchX + 15) & ~(size_t)15));
   const int i0 = blockIdx.x * kPatchX, j0 = blockIdx.y * kPatchY;
   const unsigned char far = (unsigned char)(R + 1);
-  for (int k = threadIdx.x; k < rows * kPatchX; k += blockDim.x)
+  if ((sx & 3) == 0)
   {
-    const int lj = k / kPatchX, li = k % kPatchX;
-    const int j = j0 - R + lj, i = i0 + li;
-    s_g[k] = (j >= 0 && j < sy && i < sx) ? g[(size_t)j * sx + i] : far;
+    // rows of g are 4-byte aligned: move the patch as words (16 per row)
+    const unsigned far4 = far * 0x01010101u;
+    unsigned *s_g4 = reinterpret_cast<unsigned *>(s_g);
+    for (int k = threadIdx.x; k < rows * (kPatchX / 4); k += blockDim.x)
+    {
+      const int lj = k / (kPatchX / 4), li = (k % (kPatchX / 4)) * 4;
+      const int j = j0 - R + lj, i = i0 + li;
+      s_g4[k] = (j >= 0 && j < sy && i < sx)
+                    ? __ldg(reinterpret_cast<const unsigned *>(g + (size_t)j * sx + i)) : far4;
+    }
+  }
+  else
+  {
+    for (int k = threadIdx.x; k < rows * kPatchX; k += blockDim.x)
+    {
+      const int lj = k / kPatchX, li = k % kPatchX;
+      const int j = j0 - R + lj, i = i0 + li;
+      s_g[k] = (j >= 0 && j < sy && i < sx) ? g[(size_t)j * sx + i] : far;
+    }
   }
   __syncthreads();
   const int R2 = R * R;
@@ -441,7 +477,7 @@ void map_build_distance_codes(MapCtx *m, double max_occ_dist)
     AMCL_LAUNCH_CHECK();
   }
   if (m->sy > 65535) AMCL_FATAL("maps taller than 65535 rows are not supported (%d)", m->sy);
-  dim3 g1((m->sx + 255) / 256, m->sy);
+  dim3 g1((m->sx + 1023) / 1024, m->sy);     // four cells per thread
   edt_row_bits<<<g1, 256, 0, st>>>(m->d_rowbits, m->sx, m->sy, words, pad, R, m->d_rowdist);
   AMCL_LAUNCH_CHECK();
   dim3 g2((m->sx + 1 + kPatchX - 1) / kPatchX, (m->sy + 1 + kPatchY - 1) / kPatchY);  // + padding
