@@ -76,8 +76,7 @@ __global__ void motion_kernel(const MotionArgs a)
   else
   {
     PhiloxStream rng(a.key, (uint64_t)(a.offset + i));
-#pragma unroll
-    for (int q = 0; q < 3; q++) g[q] = rng.gaussian(a.k[3 + q]);
+    rng.gaussian3(a.k[3], a.k[4], a.k[5], g);
   }
 
   if (a.model == amcl::ODOM_MODEL_DIFF || a.model == amcl::ODOM_MODEL_DIFF_CORRECTED)
@@ -116,8 +115,7 @@ __global__ void gaussian_init_kernel(Particle *set, int n, double m0, double m1,
   if (i >= n) return;
   PhiloxStream rng(key, (uint64_t)i);
   double r[3];
-#pragma unroll
-  for (int q = 0; q < 3; q++) r[q] = rng.gaussian(cr_cd[9 + q]);
+  rng.gaussian3(cr_cd[9], cr_cd[10], cr_cd[11], r);
   Particle s;
   double mean[3] = {m0, m1, m2};
   double out[3];
