@@ -1227,7 +1227,7 @@ static void build_histogram(PfCtx *c, int count)
 }
 
 // Labels + statistics for samples [0, n) of set `which`; the histogram
-// (d_keys/d_slot/d_flag/d_hash) must describe at least those samples.
+// (d_slot and the bin table) must describe at least those samples.
 static void cluster_and_stats(PfCtx *c, int which, int n)
 {
   // Labelling runs on the whole (replicated) histogram on every rank and is
