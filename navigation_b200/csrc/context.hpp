@@ -178,6 +178,7 @@ struct PfCtx
   unsigned int *d_rootlist = nullptr;  // cluster roots + their earliest samples (short-list ranking)
   int *d_bucket_index = nullptr;  // bucket index of the cumulative table (resample_dev.cu)
   size_t bucket_cap = 0;
+  double *d_logsum = nullptr;     // beam skipping: per-particle log-likelihood over all beams (first pass)
   double *d_cloud = nullptr;      // packed PoseArray for the caller (amclb200_pf_pack_cloud)
   size_t cloud_cap = 0;
   int skip_cap = 0;
@@ -219,7 +220,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
                             const double laser_pose[3], const LaserScanHost &scan,
                             const std::vector<double> &lut, const int *mask_or_null,
                             int *agree_counts_or_null,
-                            const std::vector<unsigned char> *agree_lut);
+                            const std::vector<unsigned char> *agree_lut, bool subtract_from_logsum = false);
 double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3],
                       const LaserScanHost &scan, double range_max, const double zp[6]);
 // pf.c:282-316 on device; returns n_effective, updates pf w_slow/w_fast

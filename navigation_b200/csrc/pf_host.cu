@@ -114,6 +114,7 @@ void pf_ctx_release(pf_t *pf)
   if (c->d_scan_tab) cudaFree(c->d_scan_tab);
   if (c->d_skip) cudaFree(c->d_skip);
   if (c->d_cloud) cudaFree(c->d_cloud);
+  if (c->d_logsum) cudaFree(c->d_logsum);
   if (c->d_bucket_index) cudaFree(c->d_bucket_index);
   if (c->d_rootlist) cudaFree(c->d_rootlist);
   if (c->d_tile_sum) cudaFree(c->d_tile_sum);

@@ -95,6 +95,8 @@ struct LfArgs
   double half_x, half_y;    // 0.5 + size/2, folded into the cell coordinate
   double *block_totals;     // one partial per CTA
   int *beam_counts;         // COUNT mode: agreements per used beam
+  double *logsum;           // COUNT mode: out, sum of log pz over ALL used beams per particle;
+                            // LFP mode, if not null: in, weight *= exp(logsum - sum over the beams given)
 };
 
 enum { MODE_LF = 0, MODE_LFP = 1, MODE_COUNT = 2 };
@@ -130,21 +132,23 @@ likelihood_field_kernel(const LfArgs a)
   int *s_counts = nullptr;
 
   const uint32_t beam_bytes = (uint32_t)a.nb_pad * (uint32_t)sizeof(double2);
-  const uint32_t lut_bytes = (LUT_IN_SMEM && MODE != MODE_COUNT) ? (uint32_t)a.ncodes_pad * 8u : 0u;
+  const uint32_t lut_bytes = LUT_IN_SMEM ? (uint32_t)a.ncodes_pad * 8u : 0u;
   bulk_stage_begin(&s_bar, beam_bytes + lut_bytes);
   if (threadIdx.x == 0)
   {
     bulk_stage_copy(s_beams, a.beams, beam_bytes, &s_bar);
-    if (LUT_IN_SMEM && MODE != MODE_COUNT) bulk_stage_copy(s_lut, a.lut, lut_bytes, &s_bar);
+    if (LUT_IN_SMEM) bulk_stage_copy(s_lut, a.lut, lut_bytes, &s_bar);
   }
   unsigned char *s_agree = nullptr;
   if (MODE == MODE_COUNT)
   {
-    // COUNT mode keeps no likelihood table; after the beams come one private
-    // row of per-beam counters per warp (beam i is only ever touched by lane
-    // i % 32 of that warp: plain read-modify-write, no atomics) and the
-    // code -> "agrees" bytes.
-    s_counts = reinterpret_cast<int *>(smem_raw + (size_t)a.nb_pad * sizeof(double2));
+    // COUNT mode (first pass of beam skipping): besides the log-likelihood sum
+    // over every beam it counts, per beam, the particles whose end point lies
+    // within beam_skip_distance of an obstacle.  After the beams and the table
+    // come one private row of per-beam counters per warp (beam i is only ever
+    // touched by lane i % 32 of that warp: plain read-modify-write, no atomics)
+    // and the code -> "agrees" bytes.
+    s_counts = reinterpret_cast<int *>(smem_raw + (size_t)a.nb_pad * sizeof(double2) + lut_bytes);
     const int rows = blockDim.x >> 5;
     for (int k = threadIdx.x; k < rows * a.nb; k += blockDim.x) s_counts[k] = 0;
     s_agree = reinterpret_cast<unsigned char *>(s_counts + rows * a.nb);
@@ -217,27 +221,29 @@ likelihood_field_kernel(const LfArgs a)
           if (p0 + q < a.n) agreeing += s_agree[c[q]];
         s_counts[(threadIdx.x >> 5) * a.nb + i] += agreeing;
       }
-      else
-      {
 #pragma unroll
-        for (int q = 0; q < kBlockP; q++) acc[q] += lut[c[q]];
-      }
+      for (int q = 0; q < kBlockP; q++) acc[q] += lut[c[q]];
     }
-    if (MODE != MODE_COUNT)
-    {
 #pragma unroll
-      for (int q = 0; q < kBlockP; q++)
+    for (int q = 0; q < kBlockP; q++)
+    {
+      const double sum = warp_sum(acc[q]);
+      if (lane == 0 && p0 + q < a.n)
       {
-        const double sum = warp_sum(acc[q]);
-        if (lane == 0 && p0 + q < a.n)
+        if (MODE == MODE_COUNT)
         {
-          // LF : p = 1 + sum pz^3          (amcl_laser.cpp:241,295,298)
-          // LFP: weight *= exp(sum log pz)  (amcl_laser.cpp:437,444)
-          const double factor = MODE == MODE_LF ? 1.0 + sum : exp(sum);
-          const double w = pw[q] * factor;
-          a.set[p0 + q].w = w;
-          warp_total += w;
+          a.logsum[p0 + q] = sum;   // the weight waits for the beam mask
+          continue;
         }
+        // LF : p = 1 + sum pz^3          (amcl_laser.cpp:241,295,298)
+        // LFP: weight *= exp(sum log pz)  (amcl_laser.cpp:437,444); after a COUNT
+        //      pass the beams given here are the ones to LEAVE OUT of its sum
+        double factor;
+        if (MODE == MODE_LF) factor = 1.0 + sum;
+        else factor = a.logsum ? exp(a.logsum[p0 + q] - sum) : exp(sum);
+        const double w = pw[q] * factor;
+        a.set[p0 + q].w = w;
+        warp_total += w;
       }
     }
   }
@@ -508,7 +514,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
                             const double laser_pose[3], const LaserScanHost &scan,
                             const std::vector<double> &lut, const int *mask_or_null,
                             int *agree_counts_or_null,
-                            const std::vector<unsigned char> *agree_lut)
+                            const std::vector<unsigned char> *agree_lut, bool subtract_from_logsum)
 {
   cudaStream_t st = globals().stream;
   const int n_all = c->host->sets[which].sample_count;
@@ -593,12 +599,18 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   const size_t lut_bytes = (size_t)ncodes_pad * 8;
   const size_t count_bytes =
       count_mode ? sizeof(int) * (size_t)(kSensorThreads / 32) * (size_t)nb + (size_t)ncodes_pad + 16 : 0;
-  const bool lut_smem = count_mode ? beam_bytes + count_bytes <= 200 * 1024
+  const bool lut_smem = count_mode ? beam_bytes + lut_bytes + count_bytes <= 200 * 1024
                                    : beam_bytes + lut_bytes <= 96 * 1024;
   if (count_mode && !lut_smem)
     AMCL_FATAL("beam skipping with %d beams needs %zu bytes of shared memory per block", nb,
-               beam_bytes + count_bytes);
-  const size_t smem = count_mode ? beam_bytes + count_bytes : beam_bytes + (lut_smem ? lut_bytes : 0);
+               beam_bytes + lut_bytes + count_bytes);
+  const size_t smem = beam_bytes + (lut_smem ? lut_bytes : 0) + count_bytes;
+  a.logsum = nullptr;
+  if (count_mode || subtract_from_logsum)
+  {
+    if (!c->d_logsum) AMCL_CUDA(cudaMalloc(&c->d_logsum, sizeof(double) * (size_t)c->alloc_samples));
+    a.logsum = c->d_logsum + lo;
+  }
 
   int grid;
   if (!c->ev_a)
@@ -1013,10 +1025,13 @@ double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t 
     return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, nullptr,
                                 nullptr, nullptr);
 
-  // Beam skipping (:446-489) as two device passes instead of the reference's
-  // N x B host scratch: pass 1 counts, per beam, the particles whose end point
-  // lies within beam_skip_distance of an obstacle; the host picks the beams;
-  // pass 2 integrates them.
+  // Beam skipping (:446-489) without the reference's N x B host scratch.  Pass 1
+  // goes over every beam once: per beam it counts the particles whose end point
+  // lies within beam_skip_distance of an obstacle, per particle it keeps the sum
+  // of log pz over ALL beams.  The host picks the beams as the reference does;
+  // pass 2 only visits the beams that are to be left out and applies
+  // weight *= exp(sum_all - sum_left_out) -- nothing but that N-sized finish when
+  // every beam is kept.
   const int slots = self->max_beams;
   std::vector<int> obs_count(slots, 0), obs_mask(slots, 0);
   for (size_t k = 0; k < scan.beam_ind.size(); k++)
@@ -1039,13 +1054,14 @@ double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t 
             (100 * self->beam_skip_error_threshold));
     error = true;
   }
-  if (error)
-    for (int b = 0; b < slots; b++) obs_mask[b] = 1;
   // Readings the scan loop skipped (max range / NaN) are not integrated in
   // either case: the reference would read stale scratch for them when `error`
   // is set (:479-482), which has no defined value.  See DESIGN.md.
-  return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, obs_mask.data(),
-                              nullptr, nullptr);
+  std::vector<int> leave_out(slots, 0);
+  if (!error)
+    for (int b = 0; b < slots; b++) leave_out[b] = obs_mask[b] ? 0 : 1;
+  return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, leave_out.data(),
+                              nullptr, nullptr, true);
 }
 
 // amcl_laser.cpp:144-213
