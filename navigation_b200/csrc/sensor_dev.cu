@@ -973,17 +973,28 @@ double AMCLLaser::LikelihoodFieldModel(AMCLLaserData *data, pf_sample_set_t *set
   if (step < 1) step = 1;
   LaserScanHost scan;
   tabulate_scan(data, step, true, m->scale, &scan);
-  // code -> pz^3 with the host libm in the reference's expression order
+  // code -> pz^3 with the host libm in the reference's expression order; the
+  // table only depends on the model parameters, range_max and the map's code
+  // table, so it is rebuilt only when one of those changes
   const double z_hit_denom = 2 * self->sigma_hit * self->sigma_hit;
   const double z_rand_mult = 1.0 / data->range_max;
-  std::vector<double> lut(m->dist_of_code.size() + 1);
-  for (size_t k = 0; k < lut.size(); k++)
+  static std::vector<double> lut;
+  static double lut_key[7] = {0, 0, 0, 0, -1, 0, 0};
+  // dist_of_code is sqrt(code) * scale for codes 0..R^2, then max_occ_dist
+  const double key[7] = {self->z_hit, self->z_rand, self->sigma_hit, data->range_max,
+                         (double)m->R, m->scale, m->max_occ_dist};
+  if (memcmp(key, lut_key, sizeof(key)) != 0)
   {
-    const double z = k < m->dist_of_code.size() ? m->dist_of_code[k] : m->max_occ_dist;
-    double pz = 0.0;
-    pz += self->z_hit * exp(-(z * z) / z_hit_denom);
-    pz += self->z_rand * z_rand_mult;
-    lut[k] = pz * pz * pz;
+    lut.assign(m->dist_of_code.size() + 1, 0.0);
+    for (size_t k = 0; k < lut.size(); k++)
+    {
+      const double z = k < m->dist_of_code.size() ? m->dist_of_code[k] : m->max_occ_dist;
+      double pz = 0.0;
+      pz += self->z_hit * exp(-(z * z) / z_hit_denom);
+      pz += self->z_rand * z_rand_mult;
+      lut[k] = pz * pz * pz;
+    }
+    memcpy(lut_key, key, sizeof(key));
   }
   return run_likelihood_field(c, which, m, 1, self->laser_pose.v, scan, lut, nullptr,
                               nullptr, nullptr);
@@ -1003,22 +1014,32 @@ double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t 
   const double z_hit_denom = 2 * self->sigma_hit * self->sigma_hit;
   const double z_rand_mult = 1.0 / data->range_max;
   const double max_dist_prob = exp(-(m->max_occ_dist * m->max_occ_dist) / z_hit_denom);
-  // code -> log(pz).  Last entry = off-map (:414-416).
-  std::vector<double> lut(m->dist_of_code.size() + 1);
-  std::vector<unsigned char> agree(((lut.size() + 1) & ~(size_t)1), 0);
-  for (size_t k = 0; k < lut.size(); k++)
+  // code -> log(pz).  Last entry = off-map (:414-416).  Cached like the
+  // likelihood_field table.
+  static std::vector<double> lut;
+  static std::vector<unsigned char> agree;
+  static double lut_key[8] = {0, 0, 0, 0, -1, 0, 0, 0};
+  const double key[8] = {self->z_hit, self->z_rand, self->sigma_hit, data->range_max,
+                         (double)m->R, m->scale, m->max_occ_dist, self->beam_skip_distance};
+  if (memcmp(key, lut_key, sizeof(key)) != 0)
   {
-    double pz = 0.0;
-    if (k < m->dist_of_code.size())
+    lut.assign(m->dist_of_code.size() + 1, 0.0);
+    agree.assign(((lut.size() + 1) & ~(size_t)1), 0);
+    for (size_t k = 0; k < lut.size(); k++)
     {
-      const double z = m->dist_of_code[k];
-      agree[k] = z < self->beam_skip_distance ? 1 : 0;   // :419-421
-      pz += self->z_hit * exp(-(z * z) / z_hit_denom);
+      double pz = 0.0;
+      if (k < m->dist_of_code.size())
+      {
+        const double z = m->dist_of_code[k];
+        agree[k] = z < self->beam_skip_distance ? 1 : 0;   // :419-421
+        pz += self->z_hit * exp(-(z * z) / z_hit_denom);
+      }
+      else
+        pz += self->z_hit * max_dist_prob;
+      pz += self->z_rand * z_rand_mult;
+      lut[k] = log(pz);
     }
-    else
-      pz += self->z_hit * max_dist_prob;
-    pz += self->z_rand * z_rand_mult;
-    lut[k] = log(pz);
+    memcpy(lut_key, key, sizeof(key));
   }
   const bool do_beamskip = self->do_beamskip && set->converged;   // :342-344
   if (!do_beamskip)
