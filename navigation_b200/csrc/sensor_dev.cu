@@ -165,7 +165,7 @@ likelihood_field_kernel(const LfArgs a)
   const uint16_t *__restrict__ code = a.code;
   const unsigned usx = (unsigned)a.sx, usy = (unsigned)a.sy;
   const unsigned k_row = a.k_row;
-  double warp_total = 0.0;  // meaningful in lane 0
+  double warp_total = 0.0;  // lanes 0 .. kBlockP-1: total weight of the particles they finished
 
   for (int p0 = warp_global * kBlockP; p0 < a.n; p0 += warp_stride * kBlockP)
   {
@@ -187,7 +187,7 @@ likelihood_field_kernel(const LfArgs a)
     {
       X0 = -kCellGuard; Y0 = -kCellGuard; st = 0.0; ct = 0.0;   // nothing of it is on the map
     }
-    double pX[kBlockP], pY[kBlockP], pc[kBlockP], ps[kBlockP], pw[kBlockP], acc[kBlockP];
+    double pX[kBlockP], pY[kBlockP], pc[kBlockP], ps[kBlockP], acc[kBlockP];
 #pragma unroll
     for (int q = 0; q < kBlockP; q++)
     {
@@ -195,7 +195,6 @@ likelihood_field_kernel(const LfArgs a)
       pY[q] = __shfl_sync(kFullMask, Y0, q);
       pc[q] = __shfl_sync(kFullMask, ct, q);
       ps[q] = __shfl_sync(kFullMask, st, q);
-      pw[q] = __shfl_sync(kFullMask, s.w, q);
       acc[q] = 0.0;
     }
 
@@ -224,25 +223,30 @@ likelihood_field_kernel(const LfArgs a)
 #pragma unroll
       for (int q = 0; q < kBlockP; q++) acc[q] += lut[c[q]];
     }
+    // Every lane receives the kBlockP totals; lane q (< kBlockP) finishes
+    // particle p0 + q, the one it loaded above, so that the exp() of the LFP
+    // model runs once per warp instead of once per particle.
+    double mine_sum = 0.0;
 #pragma unroll
     for (int q = 0; q < kBlockP; q++)
     {
       const double sum = warp_sum(acc[q]);
-      if (lane == 0 && p0 + q < a.n)
+      if ((lane & (kBlockP - 1)) == q) mine_sum = sum;
+    }
+    if (lane < kBlockP && p0 + lane < a.n)
+    {
+      if (MODE == MODE_COUNT)
+        a.logsum[p0 + lane] = mine_sum;   // the weight waits for the beam mask
+      else
       {
-        if (MODE == MODE_COUNT)
-        {
-          a.logsum[p0 + q] = sum;   // the weight waits for the beam mask
-          continue;
-        }
         // LF : p = 1 + sum pz^3          (amcl_laser.cpp:241,295,298)
         // LFP: weight *= exp(sum log pz)  (amcl_laser.cpp:437,444); after a COUNT
         //      pass the beams given here are the ones to LEAVE OUT of its sum
         double factor;
-        if (MODE == MODE_LF) factor = 1.0 + sum;
-        else factor = a.logsum ? exp(a.logsum[p0 + q] - sum) : exp(sum);
-        const double w = pw[q] * factor;
-        a.set[p0 + q].w = w;
+        if (MODE == MODE_LF) factor = 1.0 + mine_sum;
+        else factor = a.logsum ? exp(a.logsum[p0 + lane] - mine_sum) : exp(mine_sum);
+        const double w = s.w * factor;
+        a.set[p0 + lane].w = w;
         warp_total += w;
       }
     }
@@ -261,7 +265,7 @@ likelihood_field_kernel(const LfArgs a)
   }
   else
   {
-    const double t = block_sum(lane == 0 ? warp_total : 0.0, s_red);
+    const double t = block_sum(lane < kBlockP ? warp_total : 0.0, s_red);
     if (threadIdx.x == 0) a.block_totals[blockIdx.x] = t;
   }
 }
