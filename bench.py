@@ -342,9 +342,12 @@ def b200_arm(args):
     peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
     hbm = json.load(open(peaks_file))["hbm_gbs"] if os.path.exists(peaks_file) else 6650.0
     traffic = None
+    l2_sectors = None
     tfile = os.path.join(ROOT, "profiles", "lf_traffic.json")
     if os.path.exists(tfile) and args.beams == N_BEAMS and args.map_size == MAP_SIZE:
-        traffic = json.load(open(tfile)).get(str(n_local))     # measured by ncu for this launch shape
+        tf = json.load(open(tfile))
+        traffic = tf.get(str(n_local))     # measured by ncu for this launch shape
+        l2_sectors = tf.get("l2_sectors_%d" % n_local)
     roofline = {
         "kernel": "likelihood_field_kernel<LF>", "bound": "l2_gather",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -365,6 +368,10 @@ def b200_arm(args):
     props = torch.cuda.get_device_properties(local)
     sm_hz = 1e6 * ((clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0)
     issue_peak = props.multi_processor_count * 4 * sm_hz * 32 / 27.0
+    if l2_sectors:
+        # actual L2 sector traffic of the launch (ncu) against the measured gather peak
+        roofline["l2_sectors"] = {"per_launch": l2_sectors, "rate_per_s": l2_sectors / (k_ms * 1e-3),
+                                  "frac_of_gather_peak": l2_sectors / (k_ms * 1e-3) / gather_rate}
     roofline["issue"] = {"issue_cycles_per_warp_eval": 27, "peak_evals_per_s": issue_peak,
                          "frac": roofline["evals_per_s"] / issue_peak,
                          "note": "4 schedulers x SMs x SM clock x 32 lanes / 27 cycles; SASS count from cuobjdump"}
