@@ -22,6 +22,7 @@
 
 #include "amcl_b200.h"
 #include "context.hpp"
+#include "edt_rows.cuh"
 
 namespace amclb200
 {
@@ -65,34 +66,7 @@ __global__ void infl_row_dist(const unsigned long long *__restrict__ bits, int a
   if (c >= aw) return;
   const int stride = words + 2 * pad;
   const unsigned long long *A = bits + (size_t)r * stride + pad;
-  const int k = c >> 6, sft = c & 63;
-  int left = R + 1, right = R + 1;
-  {
-    unsigned long long w = A[k] << (63 - sft);
-    int base = 0, kk = k, have = sft + 1;
-    for (;;)
-    {
-      if (w) { left = base + __clzll((long long)w); break; }
-      base += have;
-      if (base > R) break;
-      w = A[--kk];
-      have = 64;
-    }
-  }
-  {
-    unsigned long long w = A[k] >> sft;
-    int base = 0, kk = k, have = 64 - sft;
-    for (;;)
-    {
-      if (w) { right = base + __ffsll((long long)w) - 1; break; }
-      base += have;
-      if (base > R) break;
-      w = A[++kk];
-      have = 64;
-    }
-  }
-  int best = left < right ? left : right;
-  if (best > R + 1) best = R + 1;
+  const int best = row_distance(A, c, R);
   g[(size_t)r * aw + c] = (unsigned char)best;
 }
 

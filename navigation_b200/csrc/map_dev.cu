@@ -21,6 +21,7 @@
 #include <unordered_map>
 
 #include "context.hpp"
+#include "edt_rows.cuh"
 
 namespace amclb200
 {
@@ -222,47 +223,6 @@ __global__ void edt_pack_rows(const int8_t *__restrict__ occ, int sx, int sy, in
     word = (unsigned long long)lo | ((unsigned long long)hi << 32);
   }
   if (lane == 0) bits[(size_t)j * stride + (w + pad)] = word;
-}
-
-// distance along the row from cell i to the nearest set bit of A (bit strings
-// with `pad` zero words on both sides), capped at R + 1
-__device__ __forceinline__ int row_distance(const unsigned long long *__restrict__ A, int i, int R)
-{
-  const int k = i >> 6, sft = i & 63;
-  // towards lower x: bits i, i-1, ... ; towards higher x: bits i, i+1, ...
-  int left = R + 1, right = R + 1;
-  {
-    unsigned long long w = A[k] << (63 - sft);          // bit i at the top
-    int base = 0;
-    int kk = k;
-    int have = sft + 1;                                  // valid bits in w
-    for (;;)
-    {
-      if (w) { left = base + __clzll((long long)w); break; }
-      base += have;
-      if (base > R) break;
-      kk--;
-      w = A[kk];
-      have = 64;
-    }
-  }
-  {
-    unsigned long long w = A[k] >> sft;                  // bit i at the bottom
-    int base = 0;
-    int kk = k;
-    int have = 64 - sft;
-    for (;;)
-    {
-      if (w) { right = base + __ffsll((long long)w) - 1; break; }
-      base += have;
-      if (base > R) break;
-      kk++;
-      w = A[kk];
-      have = 64;
-    }
-  }
-  int best = left < right ? left : right;
-  return best > R + 1 ? R + 1 : best;
 }
 
 // One thread per four neighbouring cells (one 4-byte store) when the row pitch
