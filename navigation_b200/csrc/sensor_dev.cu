@@ -318,23 +318,40 @@ __device__ __forceinline__ int floor_div_small(int t, int d, float inv_d)
 // entirely free (word == 0; cells outside the map count as blocked in edge
 // tiles) the walk therefore jumps straight to the first cell outside the tile --
 // the same cells are visited afterwards, in the same state.
-__device__ __forceinline__ double cast_ray(const BeamArgs &a, int x0, int y0, int x1, int y1)
+//
+// The walk is a resumable state: begin() sets a ray up, visit() performs ONE
+// iteration of the reference's loop (test a cell, then jump or step) and returns
+// true with `range` set when the ray is finished.
+struct RayWalk
 {
-  const bool steep = abs(y1 - y0) > abs(x1 - x0);
-  if (steep)
+  int x0, y0, x1, x, y, err, dx, dy, xs, ys, cur_tile;
+  bool steep, can_jump;
+  float inv_2dx, inv_2dy;
+  uint64_t word;
+  double range;
+
+  __device__ __forceinline__ void begin(int ax0, int ay0, int ax1, int ay1)
   {
-    int t = x0; x0 = y0; y0 = t;
-    t = x1; x1 = y1; y1 = t;
+    steep = abs(ay1 - ay0) > abs(ax1 - ax0);
+    if (steep)
+    {
+      int t = ax0; ax0 = ay0; ay0 = t;
+      t = ax1; ax1 = ay1; ay1 = t;
+    }
+    x0 = ax0; y0 = ay0; x1 = ax1;
+    dx = abs(ax1 - ax0);
+    dy = abs(ay1 - ay0);
+    xs = ax0 < ax1 ? 1 : -1;
+    ys = ay0 < ay1 ? 1 : -1;
+    x = ax0; y = ay0; err = 0;
+    cur_tile = -1;
+    word = 0;
+    can_jump = dx > 0 && dx < (1 << 18);
+    inv_2dx = can_jump ? 1.0f / (float)(2 * dx) : 0.0f;
+    inv_2dy = (can_jump && dy > 0) ? 1.0f / (float)(2 * dy) : 0.0f;
   }
-  const int dx = abs(x1 - x0), dy = abs(y1 - y0);
-  const int xs = x0 < x1 ? 1 : -1, ys = y0 < y1 ? 1 : -1;
-  int x = x0, y = y0, err = 0;
-  int cur_tile = -1;
-  uint64_t word = 0;
-  const bool can_jump = dx > 0 && dx < (1 << 18);      // keeps every intermediate below 2^24
-  const float inv_2dx = can_jump ? 1.0f / (float)(2 * dx) : 0.0f;
-  const float inv_2dy = (can_jump && dy > 0) ? 1.0f / (float)(2 * dy) : 0.0f;
-  for (;;)
+
+  __device__ __forceinline__ bool visit(const BeamArgs &a)
   {
     const int ci = steep ? y : x, cj = steep ? x : y;
     bool stop = !((unsigned)ci < (unsigned)a.sx && (unsigned)cj < (unsigned)a.sy);
@@ -348,29 +365,38 @@ __device__ __forceinline__ double cast_ray(const BeamArgs &a, int x0, int y0, in
       }
       if (word == 0ull && can_jump)
       {
-        const int rem = (x1 + xs - x) * xs;                       // steps until the walk's own end
-        int k = xs > 0 ? 8 - (x & 7) : (x & 7) + 1;               // steps until x leaves the tile
+        const int rem = (x1 + xs - x) * xs;
+        int k = xs > 0 ? 8 - (x & 7) : (x & 7) + 1;
         if (dy > 0)
         {
-          const int my = ys > 0 ? 8 - (y & 7) : (y & 7) + 1;      // minor advances until y leaves it
-          const int num = my * 2 * dx - dx - 2 * err;             // smallest k with m(k) >= my: ceil(num / 2dy)
+          const int my = ys > 0 ? 8 - (y & 7) : (y & 7) + 1;
+          const int num = my * 2 * dx - dx - 2 * err;
           k = min(k, floor_div_small(num + 2 * dy - 1, 2 * dy, inv_2dy));
         }
-        if (k > rem) return a.range_max;                           // the walk ends inside the free tile
+        if (k > rem)
+        {
+          range = a.range_max;
+          return true;
+        }
         const int m = floor_div_small(2 * (err + k * dy) + dx, 2 * dx, inv_2dx);
         x += k * xs;
         y += m * ys;
         err += k * dy - m * dx;
-        continue;
+        return false;
       }
       stop = (word >> (((cj & 7) << 3) | (ci & 7))) & 1ull;
     }
     if (stop)
     {
       const int ddx = x - x0, ddy = y - y0;
-      return sqrt((double)((long long)ddx * ddx + (long long)ddy * ddy)) * a.scale;
+      range = sqrt((double)((long long)ddx * ddx + (long long)ddy * ddy)) * a.scale;
+      return true;
     }
-    if (x == x1 + xs) return a.range_max;
+    if (x == x1 + xs)
+    {
+      range = a.range_max;
+      return true;
+    }
     x += xs;
     err += dy;
     if (2 * err >= dx)
@@ -378,8 +404,27 @@ __device__ __forceinline__ double cast_ray(const BeamArgs &a, int x0, int y0, in
       y += ys;
       err -= dx;
     }
+    return false;
   }
+};
+
+__device__ __forceinline__ double cast_ray(const BeamArgs &a, int x0, int y0, int x1, int y1)
+{
+  RayWalk ray;
+  ray.begin(x0, y0, x1, y1);
+  while (!ray.visit(a)) {}
+  return ray.range;
 }
+
+// Warp per particle.  The rays of a warp end at different cells; with one ray
+// per lane per round half of the lanes idle on average (ncu).  Here the warp
+// hands out beams in order: whenever kRefillIdle lanes have finished their
+// rays, the idle lanes take the next beams (neighbouring beams still go to the
+// same warp at the same time, so their tile loads stay coherent), walk for a few
+// visits, and so on.  Ranges land in a per-warp shared array indexed by beam;
+// the mixture likelihood is then evaluated as uniform work in beam order.
+constexpr int kRefillIdle = 16;
+constexpr int kVisitsPerRound = 8;
 
 __global__ void __launch_bounds__(kSensorThreads) beam_model_kernel(const BeamArgs a)
 {
@@ -397,6 +442,7 @@ __global__ void __launch_bounds__(kSensorThreads) beam_model_kernel(const BeamAr
   const int warps_per_block = blockDim.x >> 5;
   const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   const int warp_stride = gridDim.x * warps_per_block;
+  double *s_rng = reinterpret_cast<double *>(smem_raw + bytes) + (size_t)(threadIdx.x >> 5) * a.nb;
   double warp_total = 0.0;
 
   for (int p = warp_global; p < a.n; p += warp_stride)
@@ -413,25 +459,55 @@ __global__ void __launch_bounds__(kSensorThreads) beam_model_kernel(const BeamAr
     const int x0 = sane ? (int)fx0 + a.sx / 2 : -1;
     const int y0 = sane ? (int)fy0 + a.sy / 2 : -1;
 
+    RayWalk ray;
+    int next = 0;          // next beam to hand out (warp-uniform)
+    int my_beam = 0;
+    bool active = false;
+    for (;;)
+    {
+      const unsigned idle_mask = __ballot_sync(kFullMask, !active);
+      const int idle = __popc(idle_mask);
+      if (next < a.nb && (idle >= kRefillIdle || idle == 32))
+      {
+        const int rank = __popc(idle_mask & ((1u << lane) - 1u));
+        if (!active && next + rank < a.nb)
+        {
+          my_beam = next + rank;
+          const double *t = s_tab + 5 * my_beam;
+          const double cdir = ct * t[1] - st * t[2];   // cos(theta + bearing)
+          const double sdir = st * t[1] + ct * t[2];
+          const double ex = floor((px + a.range_max * cdir - a.ox) / a.scale + 0.5);
+          const double ey = floor((py + a.range_max * sdir - a.oy) / a.scale + 0.5);
+          ray.begin(x0, y0, (int)fmin(fmax(ex, -kCellGuard), kCellGuard) + a.sx / 2,
+                    (int)fmin(fmax(ey, -kCellGuard), kCellGuard) + a.sy / 2);
+          active = true;
+        }
+        next = min(a.nb, next + idle);
+      }
+      else if (idle == 32)
+        break;               // nothing in flight and nothing left to hand out
+#pragma unroll 1
+      for (int v = 0; v < kVisitsPerRound; v++)
+        if (active && ray.visit(a))
+        {
+          s_rng[my_beam] = ray.range;
+          active = false;
+        }
+    }
+    __syncwarp();
+
     double acc = 0.0;
     for (int i = lane; i < a.nb; i += 32)
     {
       const double *t = s_tab + 5 * i;
-      const double obs_range = t[0];
-      const double cdir = ct * t[1] - st * t[2];   // cos(theta + bearing)
-      const double sdir = st * t[1] + ct * t[2];
-      const double ex = floor((px + a.range_max * cdir - a.ox) / a.scale + 0.5);
-      const double ey = floor((py + a.range_max * sdir - a.oy) / a.scale + 0.5);
-      const int x1 = (int)fmin(fmax(ex, -kCellGuard), kCellGuard) + a.sx / 2;
-      const int y1 = (int)fmin(fmax(ey, -kCellGuard), kCellGuard) + a.sy / 2;
-      const double map_range = cast_ray(a, x0, y0, x1, y1);
       // amcl_laser.cpp:179-196
-      const double z = obs_range - map_range;
+      const double z = t[0] - s_rng[i];
       double pz = a.z_hit * exp(-(z * z) / a.hit_denom);
       if (z < 0) pz += t[3];
       pz += t[4];
       acc += pz * pz * pz;
     }
+    __syncwarp();
     const double sum = warp_sum(acc);
     if (lane == 0)
     {
@@ -722,7 +798,9 @@ double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3]
   a.range_max = range_max;
   a.z_hit = zp[0];
   a.hit_denom = 2 * zp[4] * zp[4];
-  const size_t smem = ((size_t)nb * 5 * 8 + 15) & ~(size_t)15;
+  // beam table, then one row of ranges per warp
+  const size_t smem = (((size_t)nb * 5 * 8 + 15) & ~(size_t)15) +
+                      (size_t)(kSensorThreads / 32) * (size_t)(nb > 0 ? nb : 1) * sizeof(double);
   int grid = persistent_grid(beam_model_kernel, kSensorThreads, smem);
   int need_blocks = (n + (kSensorThreads / 32) - 1) / (kSensorThreads / 32);
   if (grid > need_blocks) grid = need_blocks > 0 ? need_blocks : 1;
