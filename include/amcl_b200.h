@@ -179,7 +179,7 @@ int amclb200_pf_pack_cloud(pf_t *pf, int stride, int max_poses, double *out);
  * radius of a LETHAL_OBSTACLE cell of the grown window gets
  * max(old, computeCost(distance to the nearest such cell)), with the
  * NO_INFORMATION / inflate_unknown rule of :253-256.  `costs` is a host pointer
- * (only the rows the update can touch are copied each way) or, with on_device
+ * (only the rectangle the update can touch is copied each way) or, with on_device
  * != 0, a device pointer.  Returns the number of cells visited (0 when the cell
  * radius is 0, as the reference returns early). */
 int amclb200_inflate_costs(unsigned char *costs, int on_device, int size_x, int size_y, int min_i,

@@ -36,7 +36,7 @@ struct InflBox
 };
 
 // One warp per 64-cell word of a seed row.
-__global__ void infl_pack_rows(const unsigned char *__restrict__ master, int size_x, InflBox b,
+__global__ void infl_pack_rows(const unsigned char *__restrict__ master, int pitch, InflBox b,
                                int words, int pad, unsigned long long *__restrict__ bits)
 {
   const int lane = threadIdx.x & 31;
@@ -48,7 +48,7 @@ __global__ void infl_pack_rows(const unsigned char *__restrict__ master, int siz
   unsigned long long word = 0ull;
   if (w >= 0 && w < words)
   {
-    const unsigned char *row = master + (size_t)(b.e_j0 + r) * size_x;
+    const unsigned char *row = master + (size_t)(b.e_j0 + r) * pitch;
     const int i0 = b.a_i0 + w * 64 + lane, i1 = i0 + 32;
     const unsigned lo = __ballot_sync(kFullMask, i0 >= b.e_i0 && i0 < b.e_i1 && row[i0] == COST_LETHAL);
     const unsigned hi = __ballot_sync(kFullMask, i1 >= b.e_i0 && i1 < b.e_i1 && row[i1] == COST_LETHAL);
@@ -73,7 +73,7 @@ __global__ void infl_row_dist(const unsigned long long *__restrict__ bits, int a
 // One thread per reachable cell.
 __global__ void infl_col_apply(const unsigned char *__restrict__ g, int aw, InflBox b, int R,
                                const unsigned char *__restrict__ cost_of_d2, int inflate_unknown,
-                               int size_x, unsigned char *master)
+                               int pitch, unsigned char *master)
 {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = b.a_j0 + blockIdx.y;
@@ -99,7 +99,7 @@ __global__ void infl_col_apply(const unsigned char *__restrict__ g, int aw, Infl
   }
   if (best > R2) return;                       // enqueue: distance > cell_inflation_radius_ (:285-286)
   const unsigned char cost = cost_of_d2[best];
-  unsigned char *cell = master + (size_t)j * size_x + (b.a_i0 + c);
+  unsigned char *cell = master + (size_t)j * pitch + (b.a_i0 + c);
   const unsigned char old_cost = *cell;
   // inflation_layer.cpp:253-256
   if (old_cost == COST_NO_INFORMATION &&
@@ -214,14 +214,18 @@ int amclb200_inflate_costs(unsigned char *costs, int on_device, int size_x, int 
 
   unsigned char *d_master = costs;
   int row0 = 0;                       // first grid row held at d_master
+  int pitch = size_x;                 // bytes between rows at d_master
   if (!on_device)
   {
-    // only the rows the update can touch cross PCIe
-    grow(s.d_rows, s.rows_cap, (size_t)ah * size_x);
-    AMCL_CUDA(cudaMemcpyAsync(s.d_rows, costs + (size_t)b.a_j0 * size_x, (size_t)ah * size_x,
-                              cudaMemcpyHostToDevice, st));
-    d_master = s.d_rows;
+    // only the rectangle the update can touch crosses PCIe; the staging buffer
+    // holds columns [a_i0, a_i1) with pitch aw, addressed through a base pointer
+    // moved back by a_i0 so that the kernels keep using grid column indices
+    grow(s.d_rows, s.rows_cap, (size_t)ah * aw);
+    AMCL_CUDA(cudaMemcpy2DAsync(s.d_rows, (size_t)aw, costs + (size_t)b.a_j0 * size_x + b.a_i0, (size_t)size_x,
+                                (size_t)aw, (size_t)ah, cudaMemcpyHostToDevice, st));
+    d_master = s.d_rows - b.a_i0;
     row0 = b.a_j0;
+    pitch = aw;
   }
   InflBox k = b;                      // the kernels index rows relative to d_master
   k.e_j0 -= row0; k.e_j1 -= row0; k.a_j0 -= row0; k.a_j1 -= row0;
@@ -232,19 +236,19 @@ int amclb200_inflate_costs(unsigned char *costs, int on_device, int size_x, int 
   AMCL_CUDA(cudaEventRecord(ev0, st));
   {
     const long long warps = (long long)rows * (words + 2 * pad);
-    infl_pack_rows<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(d_master, size_x, k, words, pad, s.d_bits);
+    infl_pack_rows<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(d_master, pitch, k, words, pad, s.d_bits);
     AMCL_LAUNCH_CHECK();
   }
   if (rows > 65535 || ah > 65535) AMCL_FATAL("update windows taller than 65535 rows are not supported");
   infl_row_dist<<<dim3((aw + 255) / 256, rows), 256, 0, st>>>(s.d_bits, aw, words, pad, R, s.d_g);
   AMCL_LAUNCH_CHECK();
   infl_col_apply<<<dim3((aw + 255) / 256, ah), 256, 0, st>>>(s.d_g, aw, k, R, s.d_lut, inflate_unknown,
-                                                             size_x, d_master);
+                                                             pitch, d_master);
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaEventRecord(ev1, st));
   if (!on_device)
-    AMCL_CUDA(cudaMemcpyAsync(costs + (size_t)b.a_j0 * size_x, s.d_rows, (size_t)ah * size_x,
-                              cudaMemcpyDeviceToHost, st));
+    AMCL_CUDA(cudaMemcpy2DAsync(costs + (size_t)b.a_j0 * size_x + b.a_i0, (size_t)size_x, s.d_rows, (size_t)aw,
+                                (size_t)aw, (size_t)ah, cudaMemcpyDeviceToHost, st));
   AMCL_CUDA(cudaStreamSynchronize(st));
   AMCL_CUDA(cudaEventElapsedTime(&s.ms_kernels, ev0, ev1));
   cudaEventDestroy(ev0);
