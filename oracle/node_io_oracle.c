@@ -118,10 +118,13 @@ int orc_pack_cloud(const double *samples, int n, int stride, int max_poses, doub
  * include/costmap_2d/inflation_layer.h; the layer cannot be compiled here
  * (roscpp, pluginlib, dynamic_reconfigure, boost).  PINNED by the known answers
  * of the reference's own tests, restated on bare grids in
- * tests/test_inflation_oracle.py (costmap_2d/test/inflation_tests.cpp:137-282:
- * testAdjacentToObstacleCanStillMove, testInflationShouldNotCreateUnknowns,
- * testCostFunctionCorrectness, testInflationOrderCorrectness with its
- * validatePointInflation property).
+ * tests/test_inflation_oracle.py (costmap_2d/test/inflation_tests.cpp:137-410,
+ * with the rostest's cost_scaling_factor = 1: testAdjacentToObstacleCanStillMove,
+ * testInflationShouldNotCreateUnknowns, testCostFunctionCorrectness,
+ * testInflationOrderCorrectness with its validatePointInflation property,
+ * testInflation3's cell counts, and -- chained with orc_image_to_grid on the
+ * reference's TenByTen.pgm -- testInflation's 20 lethal / 28 inscribed cells and
+ * testInflation2's L-shape).
  */
 enum { ORC_NO_INFORMATION = 255, ORC_LETHAL = 254, ORC_INSCRIBED = 253, ORC_FREE = 0 }; /* cost_values.h:42-45 */
 

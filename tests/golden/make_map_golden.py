@@ -7,7 +7,8 @@ material (run in the build container, where /root/reference is mounted):
   * the expected OccupancyGrid contents from map_server/test/test_constants.cpp
     (g_valid_image_content, tmap2::g_valid_image_content) and the loader
     parameters the tests use (utest.cpp:48,68; testmap2.yaml);
-  * the value counts utest.cpp:121-152 expects for spectrum.png.
+  * the value counts utest.cpp:121-152 expects for spectrum.png;
+  * the pixels of costmap_2d/test/TenByTen.pgm, the static map of costmap_2d's inflation tests.
 """
 import os
 import re
@@ -30,6 +31,10 @@ def main():
     out = {}
     for f in ("testmap.png", "testmap.bmp", "testmap2.png", "spectrum.png"):
         out["pixels_" + f.replace(".", "_")] = np.array(Image.open(os.path.join(REF, f)))
+    # costmap_2d's static test map (costmap_2d/test/TenByTen.pgm + .yaml: negate 0, occupied 0.65, free 0.196),
+    # the map under inflation_tests.cpp's testInflation / testInflation2
+    out["pixels_tenbyten_pgm"] = np.array(Image.open("/root/reference/costmap_2d/test/TenByTen.pgm"))
+    out["params_tenbyten"] = np.array([0, 0.65, 0.196])
     out["expect_testmap"] = content("g_valid_image_content", first).reshape(10, 10)
     out["expect_testmap2"] = content("g_valid_image_content", second).reshape(12, 12)
     # utest.cpp:48,68 : negate false, occ 0.65, free 0.1, default mode TRINARY

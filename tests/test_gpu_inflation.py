@@ -37,26 +37,55 @@ def grid_with(shape, lethal):
     return g
 
 
+W = 1.0    # costmap_2d/test/inflation_tests.launch:4 sets inflation/cost_scaling_factor = 1
+
+
 def test_reference_test_cases(gpu_lib):
-    """inflation_tests.cpp:137-282 on the GPU output."""
-    out = gpu_inflate(gpu_lib, grid_with((10, 10), [(0, 0)]), None, 1.0, 2.1, 4.1)
+    """inflation_tests.cpp:137-282 and :377-410 on the GPU output."""
+    out = gpu_inflate(gpu_lib, grid_with((10, 10), [(0, 0)]), None, 1.0, 2.1, 4.1, W)
     assert out[0, 0] == LETHAL and out[0, 1] == INSCRIBED and out[0, 2] == INSCRIBED
     assert out[0, 3] < INSCRIBED and out[1, 2] < INSCRIBED and out[1, 1] == INSCRIBED
     assert np.sum(out == NO_INFORMATION) == 0
-    out = gpu_inflate(gpu_lib, grid_with((100, 100), [(50, 50)]), None, 1.0, 5.0, 10.5)
+    out = gpu_inflate(gpu_lib, grid_with((100, 100), [(50, 50)]), None, 1.0, 5.0, 10.5, W)
     for i in range(0, 6):
         for (x, y) in ((50 + i, 50), (50 - i, 50), (50, 50 + i), (50, 50 - i)):
             assert out[y, x] >= INSCRIBED
     for i in range(6, 12):
-        assert out[50, 50 + i] == oracle.port().orc_inflation_cost(float(i), 1.0, 5.0, 10.0)
-    out = gpu_inflate(gpu_lib, grid_with((10, 10), [(4, 4), (5, 5)]), None, 1.0, 2.1, 4.1)
+        assert out[50, 50 + i] == oracle.port().orc_inflation_cost(float(i), 1.0, 5.0, W)
+    out = gpu_inflate(gpu_lib, grid_with((10, 10), [(4, 4), (5, 5)]), None, 1.0, 2.1, 4.1, W)
     for (mx, my) in ((4, 4), (5, 5)):                       # validatePointInflation
         for y in range(10):
             for x in range(10):
                 d = np.hypot(x - mx, y - my)
                 if d <= 4.1:
-                    assert out[y, x] >= oracle.port().orc_inflation_cost(float(d), 1.0, 2.1, 10.0)
-    assert np.array_equal(out, oracle.inflate(grid_with((10, 10), [(4, 4), (5, 5)]), None, 1.0, 2.1, 4.1))
+                    assert out[y, x] >= oracle.port().orc_inflation_cost(float(d), 1.0, 2.1, W)
+    assert np.array_equal(out, oracle.inflate(grid_with((10, 10), [(4, 4), (5, 5)]), None, 1.0, 2.1, 4.1, W))
+    # testInflation3 (:377-410): counts after one update, no change after a second
+    out = gpu_inflate(gpu_lib, grid_with((10, 10), [(5, 5)]), None, 1.0, 1.0, 3.0, W)
+    assert np.sum(out != 0) == 29 and np.sum(out == LETHAL) == 1 and np.sum(out == INSCRIBED) == 4
+    assert np.array_equal(gpu_inflate(gpu_lib, out, None, 1.0, 1.0, 3.0, W), out)
+
+
+def test_loader_and_inflation_chained_on_the_static_test_map(gpu_lib):
+    """inflation_tests.cpp:284-303 and :348-372: TenByTen.pgm through the device map
+    ingest, 100 -> lethal as StaticLayer does, then the device inflation: 20 lethal and
+    28 inscribed cells, and the L-shape assertions of testInflation2."""
+    import ctypes as C
+    import os
+    g = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "map_server_golden.npz")))
+    px = np.ascontiguousarray(g["pixels_tenbyten_pgm"], dtype=np.uint8)
+    negate, occ_th, free_th = g["params_tenbyten"]
+    grid = np.empty(px.shape, dtype=np.int8)
+    m = gpu_lib.amclb200_map_from_image(px.ctypes.data, px.shape[1], px.shape[0], px.shape[1], 1, 0, 1.0,
+                                        (C.c_double * 3)(0, 0, 0), int(negate), occ_th, free_th, 0, grid.ctypes.data)
+    gpu_lib.map_free(m)
+    master = np.where(grid == 100, LETHAL, 0).astype(np.uint8)
+    out = gpu_inflate(gpu_lib, master, None, 1.0, 1.0, 1.0, W)
+    assert np.sum(out == LETHAL) == 20 and np.sum(out == INSCRIBED) == 28
+    for (x, y) in ((1, 1), (2, 1), (2, 2)):
+        master[y, x] = LETHAL
+    out = gpu_inflate(gpu_lib, master, None, 1.0, 1.0, 1.0, W)
+    assert out[3, 2] == INSCRIBED and out[3, 3] == INSCRIBED
 
 
 @pytest.mark.parametrize("seed,inflate_unknown,on_device", [(0, False, False), (1, True, False), (2, False, True)])
