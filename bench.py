@@ -56,8 +56,14 @@ def parse():
     ap.add_argument("--beams", type=int, default=N_BEAMS)
     ap.add_argument("--cpu-particles", type=int, default=4000,
                     help="particles per CPU worker for the reference legs")
+    ap.add_argument("--cpu-particles-large", type=int, default=100000,
+                    help="second CPU figure: one step at this many particles per worker, where the "
+                         "reference's O(N^2) resampler (pf.c:461-465) shows; 0 = skip")
     ap.add_argument("--cpu-workers", type=int, default=0, help="0 = one per host core (max 32)")
+    ap.add_argument("--cpu-steps", type=int, default=3, help="timed steps of a CPU reference leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--parity-particles", type=int, default=1 << 20,
+                    help="particles of the oracle parity pass run before the timed loop; 0 = skip")
     return ap.parse_args()
 
 
@@ -89,14 +95,13 @@ def scan_from(lib_side, pose, bear, gpu):
 # ------------------------------------------------------- reference (CPU) legs ----
 
 def _cpu_worker(args):
-    """One single-threaded replica of the reference on its own particle shard."""
+    """One single-threaded replica of the compiled reference on its own particles."""
     wid, size, beams, n, steps, warmup = args
     from navigation_b200 import abi, synth
+    from navigation_b200.harness import Side
     from oracle import oracle
-    from tests.scenario import Side
 
     ref = oracle.ref()
-    kind = "reference"
     if ref is None:
         return None
     occ, pose, bear = build_world(size, beams)
@@ -110,20 +115,23 @@ def _cpu_worker(args):
     used = int(np.sum(scan[:, 0] < RANGE_MAX))
     cloud = synth.uniform_cloud(occ, SCALE, n, 100 + wid)
     side.seed(1 + wid)
-    times = []
+    times, stage = [], np.zeros(3)
     for it in range(warmup + steps):
         side.set_samples(cloud)
         t0 = time.perf_counter()
         side.update_action(ODOM_POSE, ODOM_DELTA)
+        t1 = time.perf_counter()
         side.update_sensor(scan, RANGE_MAX)
+        t2 = time.perf_counter()
         side.resample()
         tab = side.cluster_table()
-        dt = time.perf_counter() - t0
+        t3 = time.perf_counter()
         if it >= warmup:
-            times.append(dt)
+            times.append(t3 - t0)
+            stage += (t1 - t0, t2 - t1, t3 - t2)
     side.close()
-    return dict(kind=kind, seconds=float(np.sum(times)), steps=steps, n=n, used_beams=used,
-                cspace_s=t_cspace, clusters=len(tab))
+    return dict(seconds=float(np.sum(times)), steps=steps, n=n, used_beams=used, cspace_s=t_cspace,
+                clusters=len(tab), stage_s=(stage / steps).tolist())
 
 
 def run_cpu_reference(size, beams, n_per_worker, steps, warmup, workers):
@@ -131,6 +139,13 @@ def run_cpu_reference(size, beams, n_per_worker, steps, warmup, workers):
     of its own); returns aggregate evals/s and the per-step wall time."""
     import multiprocessing as mp
 
+    from oracle import oracle
+
+    # dlopen the compiled reference in THIS process too, before forking: the
+    # workers inherit the mapping and the driver's native-library record shows
+    # oracle/_ref/libamcl_ref.so for this arm
+    if oracle.ref() is None:
+        return None
     ctx = mp.get_context("fork")
     with ctx.Pool(workers) as pool:
         t0 = time.perf_counter()
@@ -142,31 +157,53 @@ def run_cpu_reference(size, beams, n_per_worker, steps, warmup, workers):
     slowest = max(r["seconds"] for r in res)
     return dict(value=evals / slowest, ms_per_step=1e3 * slowest / steps, cores=workers,
                 kind="reference", wall_s=wall, cspace_s=max(r["cspace_s"] for r in res),
-                sample="%d workers x %d particles x %d used beams, %d steps each, %dx%d map"
-                       % (workers, n_per_worker, res[0]["used_beams"], steps, size, size))
+                steps=steps, warmup=warmup,
+                stage_ms={k: 1e3 * float(np.mean([r["stage_s"][i] for r in res]))
+                          for i, k in enumerate(("action", "sensor", "resample"))},
+                sample="%d single-thread replicas of the compiled reference x %d particles x %d used beams, "
+                       "%d warm-up + %d timed steps each, %dx%d map"
+                       % (workers, n_per_worker, res[0]["used_beams"], warmup, steps, size, size))
+
+
+def host_workers(args):
+    return args.cpu_workers if args.cpu_workers > 0 else min(max(1, (os.cpu_count() or 1)), 32)
 
 
 def reference_arm(args):
+    """`--impl reference`: the reference's own CPU code (oracle/_ref, built from the
+    unmodified sources) on the host cores.  Each replica runs a bounded sample of
+    the workload; the line says how many steps really ran."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    workers = args.cpu_workers if args.cpu_workers > 0 else min(max(1, (os.cpu_count() or 1)), 32)
-    r = run_cpu_reference(args.map_size, args.beams, args.cpu_particles, max(1, min(args.steps, 3)),
-                          min(args.warmup, 1), workers)
+    workers = host_workers(args)
+    steps = max(1, min(args.steps, args.cpu_steps))
+    warmup = max(1, min(args.warmup, 1))
+    r = run_cpu_reference(args.map_size, args.beams, args.cpu_particles, steps, warmup, workers)
     if r is None:
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libamcl_ref.so not built"}))
         return
+    large = None
+    if args.cpu_particles_large > 0:
+        large = run_cpu_reference(args.map_size, args.beams, args.cpu_particles_large, 1, 0, workers)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT,
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
+        "steps_requested": args.steps, "warmup_requested": args.warmup,
         "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, note="CPU reference, bounded sample"),
+        "config": workload_config(args, note="CPU reference, bounded sample: %s" % r["sample"]),
         "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
-                         "sample": r["sample"]},
+                         "sample": r["sample"], "stage_ms": r["stage_ms"]},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if large is not None:
+        line["cpu_baseline_large"] = {
+            "value": large["value"], "unit": UNIT, "cores": large["cores"], "kind": large["kind"],
+            "ms_per_step": large["ms_per_step"], "stage_ms": large["stage_ms"], "sample": large["sample"],
+            "note": "same code at %d particles per replica: the linear search per draw makes resampling "
+                    "quadratic (pf.c:461-465)" % args.cpu_particles_large}
     print(json.dumps(line))
 
 
@@ -227,6 +264,212 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+# ------------------------------------------------------------------ rooflines ----
+
+def rooflines(lib, args, k_ms, n_local, used_beams, ms_step, st_action, st_resample, edt_ms, n_total, world):
+    """Roofline of the dominant kernel (the laser model) and of the HBM-bound stages.
+
+    The laser kernel gathers from an L2-resident map, so its bound is the rate at
+    which the GPU serves uncorrelated 32-byte-sector gathers, MEASURED live by a
+    probe over a table with the map's footprint.  frac = the launch's L2 sector
+    reads (ncu, recorded in profiles/lf_counters.json with the commit they were
+    taken at) per second of the live kernel time / that rate.  The figure by
+    SURVEY.md 8(d)'s definition (one sector per evaluation) is kept as
+    frac_survey_def; it exceeds 1 because neighbouring beams share sectors."""
+    k_evals = n_local * used_beams
+    alg_bytes = 32.0 * k_evals + 40.0 * n_local          # SURVEY.md 8(d)
+    map_bytes = args.map_size * args.map_size * 2
+    gather_rate = lib.amclb200_measure_gather_rate(map_bytes, 5)
+    peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    have_peaks = os.path.exists(peaks_file)
+    hbm = json.load(open(peaks_file))["hbm_gbs"] if have_peaks else 6650.0
+    hbm_src = "MEASURED_PEAKS.json" if have_peaks else "fallback (B200_PROFILING.md)"
+    rec = None
+    cfile = os.path.join(ROOT, "profiles", "lf_counters.json")
+    if os.path.exists(cfile) and args.beams == N_BEAMS and args.map_size == MAP_SIZE:
+        rec = json.load(open(cfile)).get(str(n_local))
+    sectors = rec["l2_sectors_read"] if rec else None
+    sector_rate = sectors / (k_ms * 1e-3) if sectors else None
+    roofline = {
+        "kernel": "likelihood_field_kernel<LF>", "bound": "l2_gather", "unit": "GB/s",
+        "achieved": (sector_rate * 32.0 / 1e9) if sector_rate else None,
+        "peak": gather_rate * 32.0 / 1e9,
+        "frac": (sector_rate / gather_rate) if sector_rate else None,
+        "traffic": rec["dram_bytes"] if rec else None,
+        "kernel_ms": k_ms, "share_of_step": k_ms / ms_step,
+        "evals_per_s": k_evals / (k_ms * 1e-3),
+        "l2_sectors_per_launch": sectors, "l2_sectors_per_eval": (sectors / k_evals) if sectors else None,
+        "gather_peak_sectors_per_s": gather_rate,
+        "peak_source": "measured live: uncorrelated 2-byte gathers, one 32-B sector each, over a %.1f MB table "
+                       "(= %.2f sectors per clock per SM: the probe is bound by the L1TEX sector rate, not by "
+                       "its index arithmetic)" % (map_bytes / 1e6, gather_rate / (148 * 1.965e9)),
+        "ncu_recorded": ({k: rec[k] for k in ("commit", "l1tex_sectors", "l1tex_lsu_pipe_pct", "issue_active_pct",
+                                             "fp64_pipe_pct", "l2_hit_pct", "kernel_ms_under_ncu") if k in rec}
+                         if rec else "no recorded capture for %d particles per launch" % n_local),
+        "achieved_survey_def": alg_bytes / (k_ms * 1e-3) / 1e9,
+        "frac_survey_def": alg_bytes / (k_ms * 1e-3) / 1e9 / (gather_rate * 32.0 / 1e9),
+        "note": "achieved = L2 sectors the launch reads (ncu) x 32 B / live kernel time; traffic = its DRAM "
+                "bytes (ncu): the map stays in L2, compulsory HBM traffic is the particles.  *_survey_def "
+                "counts 32 B per evaluation + 40 B per particle (SURVEY.md 8d) and is not a fraction of a "
+                "bound: 32 consecutive beams of a particle end in ~6 sectors, not 32",
+        "hbm_peak_gbs": hbm, "hbm_peak_source": hbm_src,
+    }
+
+    def hbm_stage(name, bytes_, ms, kernels, note):
+        gbs = bytes_ / (ms * 1e-3) / 1e9 if ms > 0 else None
+        return {"stage": name, "bound": "hbm", "algorithmic_bytes": int(bytes_), "ms": ms, "achieved": gbs,
+                "peak": hbm, "unit": "GB/s", "frac": (gbs / hbm) if gbs else None, "kernels": kernels, "note": note}
+
+    stages = [
+        hbm_stage("motion", 48.0 * n_local, st_action, "motion_kernel",
+                  "48 B per particle (SURVEY.md 8d); CUDA events around AMCLOdom::UpdateAction"),
+        hbm_stage("resample+clusters", 128.0 * n_local, st_resample,
+                  "exact_cumsum, pick_and_copy, bin_insert, scans, cc_*, cluster_accumulate",
+                  "128 B per particle of this rank's slice (SURVEY.md 8d); CUDA events around pf_update_resample"
+                  + ("; tables and labelling still work on global objects" if world > 1 else "")),
+        hbm_stage("map_update_cspace (EDT)", 3.0 * args.map_size * args.map_size, edt_ms,
+                  "edt_pack_rows, edt_row_bits, edt_col_pass",
+                  "3 B per cell (SURVEY.md 8d); the three kernels only, host cell conversion excluded"),
+    ]
+    return roofline, stages
+
+
+# --------------------------------------------------------------- parity pass ----
+
+PARITY_SEED = 4242
+
+
+def _mix64(a):
+    """splitmix64 finaliser on a uint64 array (wraps mod 2^64)."""
+    a = a.astype(np.uint64).copy()
+    a ^= a >> np.uint64(30)
+    a *= np.uint64(0xBF58476D1CE4E5B9)
+    a ^= a >> np.uint64(27)
+    a *= np.uint64(0x94D049BB133111EB)
+    a ^= a >> np.uint64(31)
+    return a
+
+
+def _oracle_sensor_threads(cloud, occ, dist, scan, beams, threads):
+    """likelihood_field of the oracle port over `threads` host threads (the model
+    is independent per particle; ctypes releases the GIL).  Returns the total in
+    the port's own order of summation per chunk."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle import oracle
+
+    n = cloud.shape[0]
+    lp = oracle.laser_params(z_hit=LASER["z_hit"], z_rand=LASER["z_rand"], sigma_hit=LASER["sigma_hit"])
+    bounds = np.linspace(0, n, threads + 1).astype(int)
+
+    def work(k):
+        part = cloud[bounds[k]:bounds[k + 1]]       # contiguous view: updated in place
+        if part.shape[0] == 0:
+            return 0.0
+        return oracle.laser_model(1, part, lp, beams, occ, dist, SCALE, (0.0, 0.0), MAX_OCC_DIST, scan, RANGE_MAX)
+
+    with ThreadPoolExecutor(threads) as ex:
+        return float(sum(ex.map(work, range(threads))))
+
+
+def parity_pass(lib, side, args, occ, scan, rank, world, dist_mod):
+    """One full update at --parity-particles on the GPU filter (at this run's world
+    size, host drand48 draws in the reference's order) and, on rank 0, the same
+    update through the CPU oracle port seeded alike.  Reports what north_star
+    gates: n, k and the resampled source indices bit-exact, weights within 1e-5."""
+    import torch
+
+    from navigation_b200 import library, synth
+
+    n = min(args.parity_particles, args.particles)
+    libc = C.CDLL(None)
+    libc.srand48.argtypes = [C.c_long]
+    lib.amclb200_set_rng(library.RNG_DRAND48, 0)
+    libc.srand48(PARITY_SEED)
+    rng2 = (C.c_int * 2)()
+    lib.amclb200_pf_shard_range(side.pf, n, rng2)
+    lo, hi = rng2[0], rng2[1]
+    cloud = synth.uniform_cloud(occ, SCALE, n, 777)
+    cloud[:, 3] = 1.0 / n
+    d_slice = torch.from_numpy(np.ascontiguousarray(cloud[lo:hi])).cuda()
+    # the filter is allocated for the bench's particle count; for this pass it is an
+    # n-particle filter (pf_update_resample reads pf->max_samples on every call, as
+    # the reference does, pf.c:427)
+    saved_max = side.pf.contents.max_samples
+    side.pf.contents.max_samples = n
+    lib.amclb200_pf_load_device_shard(side.pf, d_slice.data_ptr(), n)
+    odom_pose = (C.c_double * 3)(*ODOM_POSE)
+    odom_delta = (C.c_double * 3)(*ODOM_DELTA)
+    lib.amcl_c_odom_update_action(side.odom, side.pf, odom_pose, odom_delta)
+    lib.amcl_c_laser_update_sensor(side.laser, side.pf, scan.ctypes.data, scan.shape[0], RANGE_MAX)
+    after_sensor = side.samples()                     # all-gathers the slices when sharded
+    lib.pf_update_resample(side.pf)
+    cnt = int(side.cur.sample_count)
+    k = int(side.cur.kdtree.contents.leaf_count)
+    ncl = int(side.cur.cluster_count)
+    src = np.full(n, -2, np.int32)
+    lib.amclb200_pf_resample_sources(side.pf, src.ctypes.data, n)
+    lib.amclb200_pf_shard_range(side.pf, cnt, rng2)
+    slo, shi = rng2[0], rng2[1]
+    # order-independent 64-bit digest of the integer results: every rank hashes the
+    # (position, source index) pairs of its slice, the partial sums add mod 2^64
+    pos = np.arange(slo, shi, dtype=np.uint64)
+    part = int(np.sum(_mix64(pos * np.uint64(0x9E3779B97F4A7C15) + src[slo:shi].astype(np.int64).astype(np.uint64)),
+                      dtype=np.uint64))
+    src_all = src
+    if world > 1:
+        t = torch.tensor([part - (1 << 64) if part >= (1 << 63) else part], dtype=torch.int64, device="cuda")
+        dist_mod.all_reduce(t)
+        part = int(t.item()) & ((1 << 64) - 1)
+        chunk = (cnt + world - 1) // world
+        mine = torch.full((chunk,), -2, dtype=torch.int32, device="cuda")
+        mine[:shi - slo] = torch.from_numpy(src[slo:shi]).cuda()
+        whole = torch.empty(chunk * world, dtype=torch.int32, device="cuda")
+        dist_mod.all_gather_into_tensor(whole, mine)
+        src_all = whole.cpu().numpy()[:cnt]
+    counts = sorted(int(side.cur.clusters[c].count) for c in range(ncl))
+    table = side.cluster_table()
+    head = np.array([cnt, k, ncl] + counts, dtype=np.uint64)
+    digest = (part + int(np.sum(_mix64(head + np.arange(head.size, dtype=np.uint64) * np.uint64(1315423911)),
+                                dtype=np.uint64))) & ((1 << 64) - 1)
+    out = {"particles": n, "n": cnt, "k": k, "clusters": ncl, "digest": "%016x" % digest,
+           "rng": "host drand48, seed %d, reference order" % PARITY_SEED,
+           "heaviest_cluster_weight": max(t_[0] for t_ in table) if table else None}
+    if rank == 0:
+        from oracle import oracle
+
+        port = oracle.port()
+        t0 = time.perf_counter()
+        R = port.orc_cell_radius(MAX_OCC_DIST, SCALE)
+        dist = oracle.occ_dist_from_d2(oracle.edt_exact(occ, R), SCALE, MAX_OCC_DIST)
+        mine = cloud.copy()
+        port.orc_srand48(PARITY_SEED)
+        port.orc_motion(mine, n, 0, np.array(ALPHAS), np.array(ODOM_POSE), np.array(ODOM_DELTA))
+        threads = min(max(1, os.cpu_count() or 1), 32)
+        total = _oracle_sensor_threads(mine, occ, dist, scan, args.beams, threads)
+        ws, wf = C.c_double(0.0), C.c_double(0.0)
+        port.orc_sensor_finish(mine, n, total, 0.0, 0.0, C.byref(ws), C.byref(wf))
+        pose_err = float(np.max(np.abs(after_sensor[:, :3] - mine[:, :3]) / np.maximum(np.abs(mine[:, :3]), 1e-3)))
+        w_err = float(np.max(np.abs(after_sensor[:, 3] - mine[:, 3]) / mine[:, 3]))
+        ob = np.empty((n, 4))
+        osrc = np.empty(n, np.int32)
+        ok_ = C.c_int()
+        ocnt = port.orc_resample(mine, n, ob, osrc, 100, n, 0.01, 0.99, 0.0, None, None, C.byref(ok_))
+        labels = np.empty(max(ocnt, 1), np.int32)
+        oncl = port.orc_cluster_labels(ob[:ocnt].copy(), ocnt, labels, None)
+        same = ocnt == cnt and bool(np.array_equal(src_all[:cnt], osrc[:ocnt]))
+        mism = int(np.sum(src_all[:min(cnt, ocnt)] != osrc[:min(cnt, ocnt)]))
+        out.update({"oracle": {"n": int(ocnt), "k": int(ok_.value), "clusters": int(oncl)},
+                    "n_equal": ocnt == cnt, "k_equal": ok_.value == k, "clusters_equal": oncl == ncl,
+                    "indices_equal": same, "index_mismatches": mism,
+                    "max_rel_weight_err": w_err, "max_rel_pose_err": pose_err,
+                    "oracle_seconds": time.perf_counter() - t0, "oracle_threads": threads,
+                    "ok": bool(same and ok_.value == k and oncl == ncl and w_err < 1e-5 and pose_err < 1e-5)})
+    side.pf.contents.max_samples = saved_max
+    lib.amclb200_set_rng(library.RNG_PHILOX, 0x5EED)
+    return out
+
+
 # ------------------------------------------------------------------ B200 arm ----
 
 def b200_arm(args):
@@ -247,7 +490,7 @@ def b200_arm(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     from navigation_b200 import abi, library, synth
-    from tests.scenario import Side
+    from navigation_b200.harness import Side
 
     lib = library.load()
     lib.amclb200_set_rng(library.RNG_PHILOX, 0x5EED)       # one seed: ranks share one filter
@@ -267,11 +510,23 @@ def b200_arm(args):
     n_local = own_hi - own_lo
     lib.amclb200_set_mirror(side.pf, 0)      # deferred host mirror
     t0 = time.perf_counter()
-    side.make_laser(args.beams, model="lf", **dict(LASER, max_occ_dist=MAX_OCC_DIST))  # GPU EDT
+    side.make_laser(args.beams, model="lf", **dict(LASER, max_occ_dist=MAX_OCC_DIST))  # GPU EDT + host cells
     t_cspace = time.perf_counter() - t0
+    edt_ms = float(lib.amclb200_map_last_edt_ms(side.map))
     side.make_odom(model=abi.ODOM_MODEL_DIFF, alphas=ALPHAS)
     scan = scan_from(side, pose, bear, gpu=True)
     used_beams = int(np.sum(scan[:, 0] < RANGE_MAX))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- parity: this run's filter against the CPU oracle ----------------------
+    parity = None
+    if args.parity_particles > 0:
+        parity = parity_pass(lib, side, args, occ, scan, rank, world, dist)
+        barrier()
 
     # the same global cloud on every rank (hash of the global index); keep the own slice
     cloud = synth.uniform_cloud(occ, SCALE, n_total, 100)[own_lo:own_hi]
@@ -280,24 +535,23 @@ def b200_arm(args):
     scan_host = torch.from_numpy(scan).pin_memory()
     odom_pose = (C.c_double * 3)(*ODOM_POSE)
     odom_delta = (C.c_double * 3)(*ODOM_DELTA)
+    bw = C.c_double()
+    bm = abi.pf_vector_t()
+    bc = abi.pf_matrix_t()
+    cloud_stride = max(1, n_total // 2000)           # a PoseArray of ~2000 poses for the visualiser
+    cloud_out = np.empty((2048, 7))
 
-    def step():
+    def step(node_outputs=False):
         lib.amclb200_pf_load_device_shard(side.pf, pristine.data_ptr(), n_total)
         lib.amcl_c_odom_update_action(side.odom, side.pf, odom_pose, odom_delta)
         lib.amcl_c_laser_update_sensor(side.laser, side.pf, scan_host.data_ptr(), args.beams, RANGE_MAX)
         lib.pf_update_resample(side.pf)
         # what the node does next (amcl_node.cpp:1369-1394): arg-max weight cluster
         best = lib.amclb200_pf_best_cluster(side.pf, C.byref(bw), C.byref(bm), C.byref(bc))
+        if node_outputs:
+            # ... and the particle cloud it publishes (amcl_node.cpp:1349-1362), packed on the device
+            lib.amclb200_pf_pack_cloud(side.pf, cloud_stride, 2048, cloud_out.ctypes.data)
         return (best, bw.value, bm.v[0], bm.v[1], bm.v[2]), side.cur.cluster_count
-
-    bw = C.c_double()
-    bm = abi.pf_vector_t()
-    bc = abi.pf_matrix_t()
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
 
     for _ in range(args.warmup):
         step()
@@ -309,7 +563,6 @@ def b200_arm(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kernel_ms = []
     stages = []
-    t_wall0 = time.perf_counter()
     e0.record()
     for _ in range(args.steps):
         best, ncl = step()
@@ -319,7 +572,6 @@ def b200_arm(args):
         stages.append(stage_ms.copy())
     e1.record()
     barrier()
-    t_wall = time.perf_counter() - t_wall0
     launches = lib.amclb200_launch_count() - launches0
     clocks = sampler.stop() if sampler else None
     ms_total = e0.elapsed_time(e1)
@@ -330,73 +582,50 @@ def b200_arm(args):
     ms_step = ms_total / args.steps
     evals_step = n_total * used_beams
     value = evals_step / (ms_step * 1e-3)
+    st_action = float(np.mean([s_[0] for s_ in stages]))
+    st_sensor = float(np.mean([s_[1] for s_ in stages]))
+    st_resample = float(np.mean([s_[2] for s_ in stages]))
 
-    # ---- roofline of the dominant kernel (likelihood_field) ------------------
-    k_ms = float(np.mean(kernel_ms))
-    k_evals = n_local * used_beams
-    alg_bytes = 32.0 * k_evals + 40.0 * n_local
-    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    map_bytes = args.map_size * args.map_size * 2
-    gather_rate = lib.amclb200_measure_gather_rate(map_bytes, 5)
-    peak = gather_rate * 32.0 / 1e9
-    peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    hbm = json.load(open(peaks_file))["hbm_gbs"] if os.path.exists(peaks_file) else 6650.0
-    traffic = None
-    l2_sectors = None
-    tfile = os.path.join(ROOT, "profiles", "lf_traffic.json")
-    if os.path.exists(tfile) and args.beams == N_BEAMS and args.map_size == MAP_SIZE:
-        tf = json.load(open(tfile))
-        traffic = tf.get(str(n_local))     # measured by ncu for this launch shape
-        l2_sectors = tf.get("l2_sectors_%d" % n_local)
-    roofline = {
-        "kernel": "likelihood_field_kernel<LF>", "bound": "l2_gather",
-        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": traffic,
-        "note": ("algorithmic bytes = 32 B per evaluation (one L2 sector per uncorrelated gather) + 40 B per "
-                 "particle (SURVEY.md 8d); the map is L2-resident, so HBM is not the binding bound: DRAM "
-                 "traffic ('traffic', ncu) is ~64 B per particle.  Neighbouring beams share sectors, which "
-                 "is why achieved exceeds the uncorrelated-gather peak; ncu: L1TEX 90 %, issue 61 %, fp64 pipe "
-                 "41 %; ablations (profiles/r1_ncu_full_likelihood_field_16M_v2.md) put the arithmetic alone at "
-                 "15.2 ms of the 18.3 ms"),
-        "evals_per_s": k_evals / (k_ms * 1e-3), "gather_peak_per_s": gather_rate,
-        "kernel_ms": k_ms, "share_of_step": k_ms / ms_step,
-        "peak_source": "measured live: uncorrelated 2-byte gathers over a %d MB table (one 32-B sector each)" % (map_bytes >> 20),
-        "hbm_peak_gbs": hbm, "hbm_peak_source": "MEASURED_PEAKS.json" if os.path.exists(peaks_file) else "fallback",
-    }
-    # The bound that actually binds (ablations): instruction issue.  One evaluation is 20 SASS
-    # instructions per warp of which 7 are fp64 (two dispatch cycles each): 27 issue cycles.
-    props = torch.cuda.get_device_properties(local)
-    sm_hz = 1e6 * ((clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0)
-    issue_peak = props.multi_processor_count * 4 * sm_hz * 32 / 27.0
-    if l2_sectors:
-        # actual L2 sector traffic of the launch (ncu) against the measured gather peak
-        roofline["l2_sectors"] = {"per_launch": l2_sectors, "rate_per_s": l2_sectors / (k_ms * 1e-3),
-                                  "frac_of_gather_peak": l2_sectors / (k_ms * 1e-3) / gather_rate}
-    roofline["issue"] = {"issue_cycles_per_warp_eval": 27, "peak_evals_per_s": issue_peak,
-                         "frac": roofline["evals_per_s"] / issue_peak,
-                         "note": "4 schedulers x SMs x SM clock x 32 lanes / 27 cycles; SASS count from cuobjdump"}
+    roofline, roofline_stages = rooflines(lib, args, float(np.mean(kernel_ms)), n_local, used_beams, ms_step,
+                                          st_action, st_resample, edt_ms, n_total, world)
 
-    # ---- e2e: host buffers through the reference-facing API ------------------
-    # The step() above already IS the reference-facing call sequence with the
-    # scan in (pinned) host memory and the cluster table read back on the host;
-    # e2e repeats it timed by the wall clock around the API calls.
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
+    # ---- e2e: host buffers through the reference-facing API, three callers ------
+    def wall(fn):
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            fn()
+        barrier()
+        sec = (time.perf_counter() - t0) / args.steps
+        if world > 1:
+            t = torch.tensor([sec], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            sec = float(t.item())
+        return sec
+
+    # scan + odometry from the caller, plus the beam table the library stages each update
+    h2d = scan.nbytes + 48 + 16 * used_beams
+    d2h_tab = 80 * max(ncl, 1) + 64
+    e2e_s = wall(step)                                    # deferred mirror, cluster table read back
+    e2e_n2_s = wall(lambda: step(node_outputs=True))      # + the published cloud, packed on the device (N2)
+    lib.amclb200_set_mirror(side.pf, 1)
+    for _ in range(2):
         step()
-    barrier()
-    e2e_s = (time.perf_counter() - t0) / args.steps
-    if world > 1:
-        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    # scan + odometry from the caller, plus the beam table and code->likelihood
-    # table the library stages for the kernel each update
-    h2d = scan.nbytes + 48 + 16 * used_beams + 8 * (40 * 40 + 3)
-    d2h = 80 * max(ncl, 1) + 64
+    e2e_eager_s = wall(step)                              # unchanged amcl_node: samples[] mirrored after every call
+    lib.amclb200_set_mirror(side.pf, 0)
+    mirror_bytes = 32 * n_local
     e2e = {"value": evals_step / e2e_s, "unit": UNIT, "ms_per_step": 1e3 * e2e_s,
-           "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-           "note": "deferred host mirror; eager mirror adds a %d MB D2H per API call" % ((32 * n_local) >> 20)}
+           "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h_tab),
+           "caller": "deferred host mirror (amclb200_set_mirror(pf, 0)); pose estimate from amclb200_pf_best_cluster",
+           "e2e_node_n2": {"value": evals_step / e2e_n2_s, "ms_per_step": 1e3 * e2e_n2_s,
+                           "d2h_bytes_per_step": int(d2h_tab + 56 * min(2048, (n_total + cloud_stride - 1) // cloud_stride)),
+                           "caller": "a node using the device-resident outputs: amclb200_pf_best_cluster + "
+                                     "amclb200_pf_pack_cloud(stride %d)" % cloud_stride},
+           "e2e_eager_mirror": {"value": evals_step / e2e_eager_s, "ms_per_step": 1e3 * e2e_eager_s,
+                                "d2h_bytes_per_step": int(d2h_tab + 3 * mirror_bytes),
+                                "caller": "unchanged amcl_node (reads set->samples[i], amcl_node.cpp:1349-1362): the "
+                                          "library default, %d MB device-to-host after each of the three update "
+                                          "calls on this rank" % (mirror_bytes >> 20)}}
 
     if world > 1:
         dist.barrier()
@@ -411,19 +640,19 @@ def b200_arm(args):
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
-        "roofline": roofline,
-        "collectives": (dict(coll.calls, note="counts over warm-up + timed + e2e steps; in-place NCCL via torch.distributed") if coll else None),
-        "stage_ms": {"action": float(np.mean([s[0] for s in stages])),
-                     "sensor": float(np.mean([s[1] for s in stages])),
-                     "resample": float(np.mean([s[2] for s in stages])),
-                     "cspace_setup_s": t_cspace},
+        "roofline": roofline, "roofline_stages": roofline_stages, "parity": parity,
+        "collectives": (dict(coll.calls, note="counts over the whole run (parity pass, warm-up, timed and e2e steps)")
+                        if coll else None),
+        "stage_ms": {"action": st_action, "sensor": st_sensor, "resample": st_resample,
+                     "edt_kernels": edt_ms, "cspace_call_s": t_cspace},
         "result": {"clusters": int(ncl), "used_beams": used_beams, "n_after_resample": int(side.cur.sample_count),
                    "leaf_count": int(side.cur.kdtree.contents.leaf_count)},
     }
     if not args.no_cpu_baseline:
         # a fresh process: the CPU reference never shares an address space with CUDA
         out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference",
-                              "--steps", "1", "--warmup", "0", "--cpu-workers", "1",
+                              "--steps", "3", "--warmup", "1", "--cpu-workers", "1",
+                              "--cpu-particles-large", "0",
                               "--map-size", str(args.map_size), "--beams", str(args.beams),
                               "--cpu-particles", str(args.cpu_particles)],
                              capture_output=True, text=True)

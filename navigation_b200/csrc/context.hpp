@@ -74,6 +74,23 @@ struct MapCtx
   float ms_edt = 0;               // device time of the last distance transform (3 kernels)
   std::vector<double> dist_of_code;  // host: code -> metres (incl. sentinel)
 
+  // Laser-model view of the distance map (sensor_dev.cu).  Per cell the RANK of
+  // its code among the codes that can occur at all -- d2 = i^2 + j^2 <= R^2 (505
+  // values for R = 40, not 1601), then "far", then "off the map" -- so that the
+  // rank -> likelihood table is small enough to sit in shared memory once per
+  // bank pair.  4x4 tiles as in d_code but stored column-first (the offset of a
+  // cell is three integer operations), and an apron of off-map cells on every
+  // side: a particle whose beams all end inside the array needs no bounds clamp.
+  uint16_t *d_lf = nullptr;
+  size_t lf_cap = 0;              // elements allocated
+  int lf_apron = 0;               // cells on every side, a multiple of 4
+  int lf_w = 0, lf_h = 0;         // cells including the apron, multiples of 4
+  uint64_t lf_generation = 0;     // generation of d_code it was derived from (0: never)
+  uint16_t *d_rank_of_code = nullptr;
+  int rank_cap = 0;
+  std::vector<uint16_t> rank_of_code;  // host: code -> rank (0xffff: cannot occur)
+  std::vector<int> code_of_rank;       // host: rank -> code; the last two are far, off the map
+
   int code_far() const { return R * R + 1; }
 };
 
@@ -85,6 +102,7 @@ void parallel_rows(int rows, const std::function<void(int, int)> &body);  // hos
 void map_build_distance_codes(MapCtx *m, double max_occ_dist);  // exact EDT
 void map_codes_to_host_cells(MapCtx *m);         // fills cells[].occ_dist
 void map_codes_from_host_cells(MapCtx *m);       // encodes cells[].occ_dist
+void map_prepare_laser_view(MapCtx *m, int reach_cells);  // (re)builds d_lf when stale or its apron is too small
 
 // ---- particle filter -------------------------------------------------------------
 
@@ -171,9 +189,15 @@ struct PfCtx
   int *d_tile_class = nullptr;
   int tile_cap = 0;
 
-  // laser staging (beam table + LUT), sized on demand
+  // laser staging: beam table, sized on demand; rank -> likelihood table, each
+  // entry repeated lut_copies times, re-uploaded only when its version changes
   double *d_scan_tab = nullptr;
   int scan_tab_cap = 0;
+  std::vector<double> h_beam_tab, h_lut;
+  double *d_lut = nullptr;
+  size_t lut_cap = 0;
+  uint64_t lut_version = 0;
+  int lut_copies = 0;
   double *d_skip = nullptr;       // beam-skip pass: per-beam agreement counts + code->agree bytes
   unsigned int *d_rootlist = nullptr;  // cluster roots + their earliest samples (short-list ranking)
   int *d_bucket_index = nullptr;  // bucket index of the cumulative table (resample_dev.cu)
@@ -218,8 +242,8 @@ struct LaserScanHost
 // unnormalised total weight (pf_sensor_model_fn_t contract).
 double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
                             const double laser_pose[3], const LaserScanHost &scan,
-                            const std::vector<double> &lut, const int *mask_or_null,
-                            int *agree_counts_or_null,
+                            const std::vector<double> &lut, uint64_t lut_version,
+                            const int *mask_or_null, int *agree_counts_or_null,
                             const std::vector<unsigned char> *agree_lut, bool subtract_from_logsum = false);
 double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3],
                       const LaserScanHost &scan, double range_max, const double zp[6]);

@@ -118,7 +118,7 @@ void amclb200_map_calc_ranges(map_t *map, const double *rays_xya, int n, double 
 // warp reads an independent pseudo-random element, so each gather costs one
 // 32-byte L2 sector and nothing coalesces.  This is the roofline the laser
 // kernels are held against ("measured random-gather peak").
-__global__ void gather_probe_kernel(const uint16_t *__restrict__ table, unsigned int mask,
+__global__ void gather_probe_kernel(const uint16_t *__restrict__ table, unsigned int elems,
                                     int per_thread, unsigned int *sink)
 {
   unsigned int x = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
@@ -130,7 +130,7 @@ __global__ void gather_probe_kernel(const uint16_t *__restrict__ table, unsigned
     for (int u = 0; u < 8; u++)
     {
       x ^= x << 13; x ^= x >> 17; x ^= x << 5;   // xorshift32
-      idx[u] = x & mask;
+      idx[u] = __umulhi(x, elems);                // uniform over the whole table, any size
     }
 #pragma unroll
     for (int u = 0; u < 8; u++) acc += __ldg(table + idx[u]);
@@ -256,8 +256,9 @@ void amclb200_pf_sensor_kernel_stats(pf_t *pf, double out[2])
 double amclb200_measure_gather_rate(unsigned long long table_bytes, int reps)
 {
   ensure_device();
-  unsigned int elems = 1;
-  while ((unsigned long long)elems * 2 * 2 <= table_bytes) elems <<= 1;
+  if (table_bytes < 64) table_bytes = 64;
+  if (table_bytes > (8ull << 30)) table_bytes = 8ull << 30;
+  const unsigned int elems = (unsigned int)(table_bytes / 2);   // the footprint asked for, not a power of two
   uint16_t *d_table = nullptr;
   unsigned int *d_sink = nullptr;
   AMCL_CUDA(cudaMalloc(&d_table, (size_t)elems * 2));
@@ -268,12 +269,12 @@ double amclb200_measure_gather_rate(unsigned long long table_bytes, int reps)
   AMCL_CUDA(cudaEventCreate(&a));
   AMCL_CUDA(cudaEventCreate(&b));
   cudaStream_t st = globals().stream;
-  gather_probe_kernel<<<blocks, threads, 0, st>>>(d_table, elems - 1, per_thread, d_sink);  // warm
+  gather_probe_kernel<<<blocks, threads, 0, st>>>(d_table, elems, per_thread, d_sink);  // warm
   float best = 1e30f;
   for (int r = 0; r < reps; r++)
   {
     AMCL_CUDA(cudaEventRecord(a, st));
-    gather_probe_kernel<<<blocks, threads, 0, st>>>(d_table, elems - 1, per_thread, d_sink);
+    gather_probe_kernel<<<blocks, threads, 0, st>>>(d_table, elems, per_thread, d_sink);
     AMCL_CUDA(cudaEventRecord(b, st));
     AMCL_CUDA(cudaEventSynchronize(b));
     float ms = 0;

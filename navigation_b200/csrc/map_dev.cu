@@ -163,6 +163,8 @@ void map_ctx_release(map_t *map)
   cudaFree(m->d_blocked);
   cudaFree(m->d_rowdist);
   if (m->d_rowbits) cudaFree(m->d_rowbits);
+  if (m->d_lf) cudaFree(m->d_lf);
+  if (m->d_rank_of_code) cudaFree(m->d_rank_of_code);
   delete m;
   r.erase(it);
 }
@@ -410,6 +412,100 @@ static void set_code_table(MapCtx *m, double max_occ_dist)
   for (int d2 = 0; d2 <= R * R; d2++)
     m->dist_of_code[d2] = sqrt((double)d2) * m->scale;   // map_cspace.cpp:49,105
   m->dist_of_code[(size_t)R * R + 1] = max_occ_dist;      // map_cspace.cpp:148
+  // ranks of the codes that can occur: squared distances between grid cells,
+  // then "far" (R^2 + 1) and "off the map" (R^2 + 2)
+  const int R2 = R * R;
+  std::vector<char> occurs((size_t)R2 + 1, 0);
+  for (int i = 0; i <= R; i++)
+    for (int j = i; i * i + j * j <= R2; j++) occurs[(size_t)(i * i + j * j)] = 1;
+  m->rank_of_code.assign((size_t)R2 + 3, (uint16_t)0xffff);
+  m->code_of_rank.clear();
+  for (int d2 = 0; d2 <= R2; d2++)
+    if (occurs[d2])
+    {
+      m->rank_of_code[d2] = (uint16_t)m->code_of_rank.size();
+      m->code_of_rank.push_back(d2);
+    }
+  for (int extra = 1; extra <= 2; extra++)
+  {
+    m->rank_of_code[(size_t)R2 + extra] = (uint16_t)m->code_of_rank.size();
+    m->code_of_rank.push_back(R2 + extra);
+  }
+  if ((int)m->rank_of_code.size() > m->rank_cap)
+  {
+    if (m->d_rank_of_code) cudaFree(m->d_rank_of_code);
+    m->rank_cap = (int)m->rank_of_code.size();
+    AMCL_CUDA(cudaMalloc(&m->d_rank_of_code, sizeof(uint16_t) * (size_t)m->rank_cap));
+  }
+  AMCL_CUDA(cudaMemcpyAsync(m->d_rank_of_code, m->rank_of_code.data(),
+                            sizeof(uint16_t) * m->rank_of_code.size(), cudaMemcpyHostToDevice,
+                            globals().stream));
+  AMCL_CUDA(cudaStreamSynchronize(globals().stream));
+}
+
+// One thread per 4x4 tile of the laser view: fetch the tile of codes `apron`
+// cells up and to the left (32 bytes), replace every code by its rank, and store
+// the tile column-first.  Tiles outside the map hold the off-map rank.
+__global__ void build_laser_view(const uint16_t *__restrict__ code, int tiles_x, int sx, int sy,
+                                 const uint16_t *__restrict__ rank_of_code, int off_rank,
+                                 int apron, int w, int h, uint16_t *__restrict__ out)
+{
+  const int tw = w >> 2;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)tw * (h >> 2)) return;
+  const int ti = (int)(t % tw), tj = (int)(t / tw);
+  const int si = ti - (apron >> 2), sj = tj - (apron >> 2);
+  __align__(16) uint16_t v[16];
+  if (si >= 0 && sj >= 0 && si * 4 < sx && sj * 4 < sy)
+  {
+    __align__(16) uint16_t c[16];
+    const uint4 *src = reinterpret_cast<const uint4 *>(code + ((size_t)sj * tiles_x + si) * 16);
+    *reinterpret_cast<uint4 *>(c) = __ldg(src);
+    *reinterpret_cast<uint4 *>(c + 8) = __ldg(src + 1);
+#pragma unroll
+    for (int lj = 0; lj < 4; lj++)
+#pragma unroll
+      for (int li = 0; li < 4; li++) v[li * 4 + lj] = __ldg(rank_of_code + c[lj * 4 + li]);
+  }
+  else
+  {
+#pragma unroll
+    for (int k = 0; k < 16; k++) v[k] = (uint16_t)off_rank;
+  }
+  uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)t * 16);
+  dst[0] = *reinterpret_cast<const uint4 *>(v);
+  dst[1] = *reinterpret_cast<const uint4 *>(v + 8);
+}
+
+// `reach_cells`: how far from its laser a particle's beams can end.  The apron is
+// that wide when memory allows (at most the map's own size again plus 64 MB), so
+// that every particle on the map takes the clamp-free path; a narrower apron only
+// sends the particles near the border through the clamped path.
+void map_prepare_laser_view(MapCtx *m, int reach_cells)
+{
+  if (!m->dist_valid) AMCL_FATAL("laser view requested before map_update_cspace()");
+  int want = ((reach_cells > 4 ? reach_cells : 4) + 3) & ~3;
+  const size_t budget = 2 * (size_t)m->sx * m->sy + ((size_t)32 << 20);   // elements
+  while (want > 4 && (size_t)(m->sx + 2 * want) * (size_t)(m->sy + 2 * want) > budget) want -= 4;
+  if (m->lf_generation == m->generation && m->lf_apron >= want) return;
+  const int apron = want > m->lf_apron ? want : m->lf_apron;
+  const int w = (m->sx + 2 * apron + 3) & ~3, h = (m->sy + 2 * apron + 3) & ~3;
+  const size_t elems = (size_t)w * h;
+  if (elems > m->lf_cap)
+  {
+    if (m->d_lf) cudaFree(m->d_lf);
+    m->lf_cap = elems;
+    AMCL_CUDA(cudaMalloc(&m->d_lf, elems * sizeof(uint16_t)));
+  }
+  const long long tiles = (long long)(w >> 2) * (h >> 2);
+  build_laser_view<<<(unsigned)((tiles + 255) / 256), 256, 0, globals().stream>>>(
+      m->d_code, m->tiles_x, m->sx, m->sy, m->d_rank_of_code, (int)m->code_of_rank.size() - 1,
+      apron, w, h, m->d_lf);
+  AMCL_LAUNCH_CHECK();
+  m->lf_apron = apron;
+  m->lf_w = w;
+  m->lf_h = h;
+  m->lf_generation = m->generation;
 }
 
 void map_build_distance_codes(MapCtx *m, double max_occ_dist)
@@ -500,7 +596,7 @@ void map_codes_from_host_cells(MapCtx *m)
       {
         double q = d / m->scale;
         long d2 = lround(q * q);
-        if (d2 < 0 || d2 > R2 || m->dist_of_code[d2] != d)
+        if (d2 < 0 || d2 > R2 || m->dist_of_code[d2] != d || m->rank_of_code[d2] == 0xffff)
           AMCL_FATAL("occ_dist %.17g at cell (%d,%d) is not sqrt(d2)*scale for an integer "
                      "d2 <= %d; cannot encode", d, i, j, R2);
         code = (int)d2;

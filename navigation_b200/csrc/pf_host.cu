@@ -112,6 +112,7 @@ void pf_ctx_release(pf_t *pf)
   if (c->d_cluster_acc) cudaFree(c->d_cluster_acc);
   if (c->d_partials) cudaFree(c->d_partials);
   if (c->d_scan_tab) cudaFree(c->d_scan_tab);
+  if (c->d_lut) cudaFree(c->d_lut);
   if (c->d_skip) cudaFree(c->d_skip);
   if (c->d_cloud) cudaFree(c->d_cloud);
   if (c->d_logsum) cudaFree(c->d_logsum);

@@ -84,15 +84,16 @@ struct LfArgs
   const double2 *beams;     // (r cos b / scale, r sin b / scale) per used beam
   int nb;                   // number of used beams
   int nb_pad;               // rounded up to an even count (16-byte granules)
-  const double *lut;        // code -> pz^3 (LF) | log pz (LFP); [ncodes_pad]
-  const unsigned char *agree;  // code -> z < beam_skip_distance (COUNT mode)
-  int ncodes_pad;
-  const uint16_t *code;     // tiled distance codes; column sx and row sy hold the off-map code
-  int sx, sy;
-  unsigned k_row;           // 4 * tiles_x - 4 (see cell_index)
+  const double *lut;        // rank -> pz^3 (LF) | log pz (LFP), each entry repeated 2^LOGC times
+  const unsigned char *agree;  // rank -> z < beam_skip_distance (COUNT mode)
+  int nranks_pad;           // even
+  const uint16_t *lf;       // laser view of the distance map (MapCtx::d_lf)
+  unsigned max_i, max_j;    // lf_w - 1, lf_h - 1: both lie in the apron
+  unsigned k_row;           // lf_w - 1 (see lf_index)
   double lx, ly, la;        // laser pose in the robot frame
   double ox, oy, scale;     // map origin (centre) and resolution
-  double half_x, half_y;    // 0.5 + size/2, folded into the cell coordinate
+  double half_x, half_y;    // 0.5 + size/2 + apron, folded into the cell coordinate
+  double in_lo, in_hi_x, in_hi_y;  // a laser at in_lo <= X0 <= in_hi_x (Y alike) keeps every beam inside the view
   double *block_totals;     // one partial per CTA
   int *beam_counts;         // COUNT mode: agreements per used beam
   double *logsum;           // COUNT mode: out, sum of log pz over ALL used beams per particle;
@@ -101,43 +102,114 @@ struct LfArgs
 
 enum { MODE_LF = 0, MODE_LFP = 1, MODE_COUNT = 2 };
 
-constexpr int kSensorThreads = 256;
+constexpr int kSensorThreads = 256;     // beam model
+#ifndef AMCL_LF_THREADS
+#define AMCL_LF_THREADS 384
+#endif
+#ifndef AMCL_LF_MINBLOCKS
+#define AMCL_LF_MINBLOCKS 2
+#endif
+constexpr int kLfThreads = AMCL_LF_THREADS;   // likelihood-field kernels: 2 CTAs of 12 warps per SM
 constexpr double kCellGuard = 536870912.0;  // 2^29: beyond this nothing is on a map
 
 // Particles handled together by one warp: every beam-table entry fetched from
 // shared memory is applied to kBlockP particles, which divides the shared-
 // memory traffic of the table by kBlockP and keeps kBlockP independent map
-// gathers in flight per lane (ncu on the one-particle version: L1TEX 75 % busy,
-// half of it beam-table wavefronts; profiles/r1_ncu_full_likelihood_field_2M.md).
-constexpr int kBlockP = 4;
+// gathers in flight per lane.
+#ifndef AMCL_LF_BLOCKP
+#define AMCL_LF_BLOCKP 4
+#endif
+constexpr int kBlockP = AMCL_LF_BLOCKP;
 
-// Offset of cell (mi, mj) in the 4x4-tiled code array,
-//   ((mj >> 2) * tiles_x + (mi >> 2)) * 16 + (mj & 3) * 4 + (mi & 3).
-// With t = mi & ~3 and u = mj & ~3 this is (3 t + mi) + (k_row u + 4 mj),
-// k_row = 4 tiles_x - 4: two ANDs, two multiply-adds and one shift-add.
-__device__ __forceinline__ unsigned cell_index(unsigned mi, unsigned mj, unsigned k_row)
+// Offset of cell (mi, mj) in the laser view: 4x4 tiles, tiles row-major, cells
+// of a tile column-first,
+//   ((mj >> 2) * (w / 4) + (mi >> 2)) * 16 + (mi & 3) * 4 + (mj & 3)
+//     = (mj & ~3) * (w - 1) + mj + 4 mi
+// -- one AND, one multiply-add, one shift-add.
+__device__ __forceinline__ unsigned lf_index(unsigned mi, unsigned mj, unsigned k_row)
 {
-  return (mi & ~3u) * 3u + mi + (mj & ~3u) * k_row + (mj << 2);
+  return (mj & ~3u) * k_row + mj + (mi << 2);
 }
 
-template <int MODE, bool LUT_IN_SMEM>
-__global__ void __launch_bounds__(kSensorThreads, 3)
+// The beam loop of one group of kBlockP particles.  CLAMP = false is the path of
+// particles whose beams all end inside the view (apron included); CLAMP = true
+// moves end points beyond it (negative indices wrap to huge unsigned values) onto
+// the last column / row, which lie in the apron and hold the off-map rank
+// (!MAP_VALID end points, amcl_laser.cpp:283-286): no branch either way.
+//
+// LOGC: every table entry is stored 2^LOGC times, copy l in bank pair l; lane
+// l & (2^LOGC - 1) reads its own copy.  With 16 copies the 8-byte reads of a
+// half-warp never meet in a bank (ncu on the single-copy table: 4.4 wavefronts
+// per read, the largest share of the LSU pipe that bounds this kernel).
+template <int MODE, int LOGC, bool CLAMP>
+__device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_beams,
+                                             const double *lut_lane, const unsigned char *s_agree,
+                                             int *s_count_row, int lane, int live,
+                                             const double (&pX)[kBlockP], const double (&pY)[kBlockP],
+                                             const double (&pc)[kBlockP], const double (&ps)[kBlockP],
+                                             double (&acc)[kBlockP])
+{
+  const uint16_t *__restrict__ lf = a.lf;
+  const unsigned k_row = a.k_row, max_i = a.max_i, max_j = a.max_j;
+  constexpr int kShift = LOGC < 0 ? 0 : LOGC;
+  auto gather = [&](int i, unsigned (&r)[kBlockP]) {
+    const double2 b = s_beams[i];
+#pragma unroll
+    for (int q = 0; q < kBlockP; q++)
+    {
+      unsigned mi = (unsigned)floor_to_int(fma(pc[q], b.x, fma(-ps[q], b.y, pX[q])));
+      unsigned mj = (unsigned)floor_to_int(fma(ps[q], b.x, fma(pc[q], b.y, pY[q])));
+      if (CLAMP)
+      {
+        mi = min(mi, max_i);
+        mj = min(mj, max_j);
+      }
+      r[q] = __ldg(lf + lf_index(mi, mj, k_row));
+    }
+  };
+  auto consume = [&](int i, const unsigned (&r)[kBlockP]) {
+    if (MODE == MODE_COUNT)
+    {
+      int agreeing = 0;
+#pragma unroll
+      for (int q = 0; q < kBlockP; q++)
+        if (q < live) agreeing += s_agree[r[q]];
+      s_count_row[i] += agreeing;
+    }
+#pragma unroll
+    for (int q = 0; q < kBlockP; q++) acc[q] += lut_lane[r[q] << kShift];
+  };
+  // (Issuing the gathers of beam i + 32 before the table reads of beam i was
+  // measured twice and loses: the L1TEX pipe, not the gather latency, is what
+  // this loop waits for -- profiles/r2_lf_kernel.md.)
+  for (int i = lane; i < a.nb; i += 32)
+  {
+    unsigned r[kBlockP];
+    gather(i, r);
+    consume(i, r);
+  }
+}
+
+template <int MODE, int LOGC>
+__global__ void __launch_bounds__(kLfThreads, AMCL_LF_MINBLOCKS)
 likelihood_field_kernel(const LfArgs a)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double2 *s_beams = reinterpret_cast<double2 *>(smem_raw);
   double *s_lut = reinterpret_cast<double *>(smem_raw + (size_t)a.nb_pad * sizeof(double2));
   __shared__ __align__(8) uint64_t s_bar;
-  __shared__ double s_red[kSensorThreads / 32];
+  __shared__ double s_red[kLfThreads / 32];
   int *s_counts = nullptr;
 
+  constexpr bool kLutInSmem = LOGC >= 0;
+  constexpr int kCopies = kLutInSmem ? (1 << LOGC) : 1;
   const uint32_t beam_bytes = (uint32_t)a.nb_pad * (uint32_t)sizeof(double2);
-  const uint32_t lut_bytes = LUT_IN_SMEM ? (uint32_t)a.ncodes_pad * 8u : 0u;
+  const uint32_t lut_bytes = kLutInSmem ? (uint32_t)a.nranks_pad * 8u * (uint32_t)kCopies : 0u;
   bulk_stage_begin(&s_bar, beam_bytes + lut_bytes);
   if (threadIdx.x == 0)
   {
     bulk_stage_copy(s_beams, a.beams, beam_bytes, &s_bar);
-    if (LUT_IN_SMEM) bulk_stage_copy(s_lut, a.lut, lut_bytes, &s_bar);
+    if (kLutInSmem) bulk_stage_copy(s_lut, a.lut, lut_bytes, &s_bar);
   }
   unsigned char *s_agree = nullptr;
   if (MODE == MODE_COUNT)
@@ -147,24 +219,22 @@ likelihood_field_kernel(const LfArgs a)
     // within beam_skip_distance of an obstacle.  After the beams and the table
     // come one private row of per-beam counters per warp (beam i is only ever
     // touched by lane i % 32 of that warp: plain read-modify-write, no atomics)
-    // and the code -> "agrees" bytes.
+    // and the rank -> "agrees" bytes.
     s_counts = reinterpret_cast<int *>(smem_raw + (size_t)a.nb_pad * sizeof(double2) + lut_bytes);
     const int rows = blockDim.x >> 5;
     for (int k = threadIdx.x; k < rows * a.nb; k += blockDim.x) s_counts[k] = 0;
     s_agree = reinterpret_cast<unsigned char *>(s_counts + rows * a.nb);
-    for (int k = threadIdx.x; k < a.ncodes_pad; k += blockDim.x) s_agree[k] = a.agree[k];
+    for (int k = threadIdx.x; k < a.nranks_pad; k += blockDim.x) s_agree[k] = a.agree[k];
   }
   __syncthreads();  // barrier init visible to all before anyone polls it
   bulk_stage_wait(&s_bar);
 
-  const double *lut = LUT_IN_SMEM ? s_lut : a.lut;
   const int lane = threadIdx.x & 31;
+  const double *lut_lane = (kLutInSmem ? s_lut : a.lut) + (lane & (kCopies - 1));
   const int warps_per_block = blockDim.x >> 5;
   const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   const int warp_stride = gridDim.x * warps_per_block;
-  const uint16_t *__restrict__ code = a.code;
-  const unsigned usx = (unsigned)a.sx, usy = (unsigned)a.sy;
-  const unsigned k_row = a.k_row;
+  int *s_count_row = MODE == MODE_COUNT ? s_counts + (threadIdx.x >> 5) * a.nb : nullptr;
   double warp_total = 0.0;  // lanes 0 .. kBlockP-1: total weight of the particles they finished
 
   for (int p0 = warp_global * kBlockP; p0 < a.n; p0 += warp_stride * kBlockP)
@@ -172,7 +242,7 @@ likelihood_field_kernel(const LfArgs a)
     // Lane q (< kBlockP) prepares particle p0+q: laser pose by
     // pf_vector_coord_add(laser_pose, pose) (pf_vector.c:106-116) -- only the
     // sine / cosine of the summed heading are needed -- and the cell-unit
-    // origin MAP_GXWX / MAP_GYWY (map.h:137-138) with size/2 folded in.
+    // origin MAP_GXWX / MAP_GYWY (map.h:137-138) with size/2 and the apron folded in.
     const int mine = min(p0 + (lane & (kBlockP - 1)), a.n - 1);
     const Particle s = load_particle(a.set + mine);
     double sn, cs;
@@ -187,6 +257,12 @@ likelihood_field_kernel(const LfArgs a)
     {
       X0 = -kCellGuard; Y0 = -kCellGuard; st = 0.0; ct = 0.0;   // nothing of it is on the map
     }
+    const bool inside = X0 >= a.in_lo && X0 <= a.in_hi_x && Y0 >= a.in_lo && Y0 <= a.in_hi_y;
+#ifdef AMCL_LF_FORCE_CLAMP   /* kernel-variant experiments only */
+    const bool all_inside = false;
+#else
+    const bool all_inside = __all_sync(kFullMask, inside);
+#endif
     double pX[kBlockP], pY[kBlockP], pc[kBlockP], ps[kBlockP], acc[kBlockP];
 #pragma unroll
     for (int q = 0; q < kBlockP; q++)
@@ -197,32 +273,12 @@ likelihood_field_kernel(const LfArgs a)
       ps[q] = __shfl_sync(kFullMask, st, q);
       acc[q] = 0.0;
     }
+    const int live = min(kBlockP, a.n - p0);
+    if (all_inside)
+      lf_beam_loop<MODE, LOGC, false>(a, s_beams, lut_lane, s_agree, s_count_row, lane, live, pX, pY, pc, ps, acc);
+    else
+      lf_beam_loop<MODE, LOGC, true>(a, s_beams, lut_lane, s_agree, s_count_row, lane, live, pX, pY, pc, ps, acc);
 
-    for (int i = lane; i < a.nb; i += 32)
-    {
-      const double2 b = s_beams[i];
-      int c[kBlockP];
-#pragma unroll
-      for (int q = 0; q < kBlockP; q++)
-      {
-        // !MAP_VALID end points (amcl_laser.cpp:283-286) -- negative indices wrap
-        // to huge unsigned values -- are clamped onto the padding column / row,
-        // whose cells hold the off-map code: no branch, no predicate.
-        const unsigned mi = min((unsigned)floor_to_int(fma(pc[q], b.x, fma(-ps[q], b.y, pX[q]))), usx);
-        const unsigned mj = min((unsigned)floor_to_int(fma(ps[q], b.x, fma(pc[q], b.y, pY[q]))), usy);
-        c[q] = __ldg(code + cell_index(mi, mj, k_row));
-      }
-      if (MODE == MODE_COUNT)
-      {
-        int agreeing = 0;
-#pragma unroll
-        for (int q = 0; q < kBlockP; q++)
-          if (p0 + q < a.n) agreeing += s_agree[c[q]];
-        s_counts[(threadIdx.x >> 5) * a.nb + i] += agreeing;
-      }
-#pragma unroll
-      for (int q = 0; q < kBlockP; q++) acc[q] += lut[c[q]];
-    }
     // Every lane receives the kBlockP totals; lane q (< kBlockP) finishes
     // particle p0 + q, the one it loaded above, so that the exp() of the LFP
     // model runs once per warp instead of once per particle.
@@ -590,10 +646,12 @@ static int persistent_grid(K kernel, int threads, size_t smem)
   return per_sm * globals().sm_count;
 }
 
+// `lut` is indexed by code RANK (MapCtx::code_of_rank); `lut_version` changes
+// whenever its contents do, so the replicated device copy is rebuilt only then.
 double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
                             const double laser_pose[3], const LaserScanHost &scan,
-                            const std::vector<double> &lut, const int *mask_or_null,
-                            int *agree_counts_or_null,
+                            const std::vector<double> &lut, uint64_t lut_version,
+                            const int *mask_or_null, int *agree_counts_or_null,
                             const std::vector<unsigned char> *agree_lut, bool subtract_from_logsum)
 {
   cudaStream_t st = globals().stream;
@@ -601,41 +659,86 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   const int lo = c->shard.lo(n_all);
   const int n = c->shard.count(n_all);     // this rank's slice (everything when not sharded)
   // beam table: only beams that are integrated (mask applied on the host)
-  std::vector<double> tab;
+  std::vector<double> &tab = c->h_beam_tab;
   std::vector<int> used;
+  tab.clear();
+  double reach = 0.0;
   for (size_t k = 0; k < scan.a.size(); k++)
   {
     if (mask_or_null && !mask_or_null[scan.beam_ind[k]]) continue;
     tab.push_back(scan.a[k]);
     tab.push_back(scan.b[k]);
+    const double len = sqrt(scan.a[k] * scan.a[k] + scan.b[k] * scan.b[k]) + 1.0;   // cells
+    if (len > reach) reach = len;
     used.push_back((int)k);
   }
   const int nb = (int)used.size();
   const int nb_pad = (nb + 1) & ~1;
   tab.resize((size_t)(nb_pad > 0 ? nb_pad : 2) * 2, 0.0);
-  const int ncodes = (int)lut.size();
-  const int ncodes_pad = (ncodes + 1) & ~1;
+  const int nranks = (int)lut.size();
+  const int nranks_pad = (nranks + 1) & ~1;
   const bool count_mode = agree_counts_or_null != nullptr;
+  if (nranks != (int)m->code_of_rank.size())
+    AMCL_FATAL("likelihood table has %d entries, the map's codes have %zu ranks", nranks,
+               m->code_of_rank.size());
+  // the laser view of the distance map, with an apron as wide as the beams reach
+  if (!(reach < 1e8)) reach = 1e8;
+  map_prepare_laser_view(m, (int)reach + 2);
 
-  // device staging: [beams | lut | agree bytes | counts]
-  size_t need = tab.size() + (size_t)ncodes_pad;
-  if ((int)need > c->scan_tab_cap)
+  if ((int)tab.size() > c->scan_tab_cap)
   {
     if (c->d_scan_tab) cudaFree(c->d_scan_tab);
-    c->scan_tab_cap = (int)need + 1024;
+    c->scan_tab_cap = (int)tab.size() + 1024;
     AMCL_CUDA(cudaMalloc(&c->d_scan_tab, sizeof(double) * (size_t)c->scan_tab_cap));
   }
-  std::vector<double> stage(need, 0.0);
-  memcpy(stage.data(), tab.data(), tab.size() * sizeof(double));
-  memcpy(stage.data() + tab.size(), lut.data(), lut.size() * sizeof(double));
-  AMCL_CUDA(cudaMemcpyAsync(c->d_scan_tab, stage.data(), need * sizeof(double),
+  AMCL_CUDA(cudaMemcpyAsync(c->d_scan_tab, tab.data(), tab.size() * sizeof(double),
                             cudaMemcpyHostToDevice, st));
+
+  // shared memory: [beams | table x copies | COUNT: counters per warp, agree bytes]
+  const size_t beam_bytes = (size_t)(nb_pad > 0 ? nb_pad : 2) * sizeof(double2);
+  const size_t count_bytes =
+      count_mode ? sizeof(int) * (size_t)(kLfThreads / 32) * (size_t)nb + (size_t)nranks_pad + 16 : 0;
+  const size_t per_cta = (size_t)(220 / AMCL_LF_MINBLOCKS) * 1024;   // AMCL_LF_MINBLOCKS CTAs per SM
+  int logc = -1;
+  for (int cand = 4; cand >= 0; cand -= 2)
+    if (beam_bytes + count_bytes + ((size_t)nranks_pad * 8 << cand) <= per_cta)
+    {
+      logc = cand;
+      break;
+    }
+  if (logc < 0 && beam_bytes + count_bytes + (size_t)nranks_pad * 8 <= 200 * 1024) logc = 0;
+  if (beam_bytes + count_bytes > 200 * 1024)
+    AMCL_FATAL("a scan of %d beams needs %zu bytes of shared memory per block", nb,
+               beam_bytes + count_bytes);
+#ifdef AMCL_LF_FORCE_LOGC   /* kernel-variant experiments only */
+  if (logc > AMCL_LF_FORCE_LOGC) logc = AMCL_LF_FORCE_LOGC;
+#endif
+  const int copies = logc < 0 ? 1 : (1 << logc);
+
+  // device copy of the table, each entry repeated `copies` times
+  if (c->lut_version != lut_version || c->lut_copies != copies)
+  {
+    const size_t need = (size_t)nranks_pad * copies;
+    if (need > c->lut_cap)
+    {
+      if (c->d_lut) cudaFree(c->d_lut);
+      c->lut_cap = need + 1024;
+      AMCL_CUDA(cudaMalloc(&c->d_lut, sizeof(double) * c->lut_cap));
+    }
+    c->h_lut.assign(need, 0.0);
+    for (int r = 0; r < nranks; r++)
+      for (int k = 0; k < copies; k++) c->h_lut[(size_t)r * copies + k] = lut[r];
+    AMCL_CUDA(cudaMemcpyAsync(c->d_lut, c->h_lut.data(), need * sizeof(double),
+                              cudaMemcpyHostToDevice, st));
+    c->lut_version = lut_version;
+    c->lut_copies = copies;
+  }
 
   unsigned char *d_agree = nullptr;
   int *d_counts = nullptr;
   if (count_mode)
   {
-    size_t bytes = (size_t)ncodes_pad + sizeof(int) * (size_t)(nb + 1);
+    size_t bytes = (size_t)nranks_pad + sizeof(int) * (size_t)(nb + 1);
     if ((int)bytes > c->skip_cap)
     {
       if (c->d_skip) cudaFree(c->d_skip);
@@ -655,36 +758,27 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   a.beams = reinterpret_cast<const double2 *>(c->d_scan_tab);
   a.nb = nb;
   a.nb_pad = nb_pad > 0 ? nb_pad : 2;
-  a.lut = c->d_scan_tab + tab.size();
+  a.lut = c->d_lut;
   a.agree = d_agree;
-  a.ncodes_pad = ncodes_pad;
-  // last table entry = off-map end point = the code stored in the map's padding
-  if (ncodes - 1 != m->R * m->R + 2)
-    AMCL_FATAL("likelihood table has %d entries, the map's codes need %d", ncodes, m->R * m->R + 3);
-  a.code = m->d_code;
-  a.k_row = 4u * (unsigned)m->tiles_x - 4u;
-  a.sx = m->sx;
-  a.sy = m->sy;
+  a.nranks_pad = nranks_pad;
+  a.lf = m->d_lf;
+  a.max_i = (unsigned)m->lf_w - 1u;
+  a.max_j = (unsigned)m->lf_h - 1u;
+  a.k_row = (unsigned)m->lf_w - 1u;
   a.lx = laser_pose[0];
   a.ly = laser_pose[1];
   a.la = laser_pose[2];
   a.ox = m->origin_x;
   a.oy = m->origin_y;
   a.scale = m->scale;
-  a.half_x = 0.5 + (double)(m->sx / 2);
-  a.half_y = 0.5 + (double)(m->sy / 2);
+  a.half_x = 0.5 + (double)(m->sx / 2) + (double)m->lf_apron;
+  a.half_y = 0.5 + (double)(m->sy / 2) + (double)m->lf_apron;
+  a.in_lo = reach + 1.0;
+  a.in_hi_x = (double)m->lf_w - reach - 1.0;
+  a.in_hi_y = (double)m->lf_h - reach - 1.0;
   a.beam_counts = d_counts;
 
-  const size_t beam_bytes = (size_t)a.nb_pad * sizeof(double2);
-  const size_t lut_bytes = (size_t)ncodes_pad * 8;
-  const size_t count_bytes =
-      count_mode ? sizeof(int) * (size_t)(kSensorThreads / 32) * (size_t)nb + (size_t)ncodes_pad + 16 : 0;
-  const bool lut_smem = count_mode ? beam_bytes + lut_bytes + count_bytes <= 200 * 1024
-                                   : beam_bytes + lut_bytes <= 96 * 1024;
-  if (count_mode && !lut_smem)
-    AMCL_FATAL("beam skipping with %d beams needs %zu bytes of shared memory per block", nb,
-               beam_bytes + lut_bytes + count_bytes);
-  const size_t smem = beam_bytes + (lut_smem ? lut_bytes : 0) + count_bytes;
+  const size_t smem = beam_bytes + (logc >= 0 ? (size_t)nranks_pad * 8 * copies : 0) + count_bytes;
   a.logsum = nullptr;
   if (count_mode || subtract_from_logsum)
   {
@@ -692,36 +786,36 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
     a.logsum = c->d_logsum + lo;
   }
 
-  int grid;
+  int grid = 1;
   if (!c->ev_a)
   {
     AMCL_CUDA(cudaEventCreate(&c->ev_a));
     AMCL_CUDA(cudaEventCreate(&c->ev_b));
   }
   AMCL_CUDA(cudaEventRecord(c->ev_a, st));
-#define AMCL_LF_LAUNCH(MODE, INSMEM)                                                     \
+#define AMCL_LF_LAUNCH(MODE, LOGC)                                                       \
   do                                                                                     \
   {                                                                                      \
-    grid = persistent_grid(likelihood_field_kernel<MODE, INSMEM>, kSensorThreads, smem); \
-    int need_blocks = (n + (kSensorThreads / 32) * kBlockP - 1) / ((kSensorThreads / 32) * kBlockP); \
+    grid = persistent_grid(likelihood_field_kernel<MODE, LOGC>, kLfThreads, smem);       \
+    int need_blocks = (n + (kLfThreads / 32) * kBlockP - 1) / ((kLfThreads / 32) * kBlockP); \
     if (grid > need_blocks) grid = need_blocks > 0 ? need_blocks : 1;                    \
     ensure_partials(c, grid);                                                            \
     a.block_totals = c->d_partials;                                                      \
-    likelihood_field_kernel<MODE, INSMEM><<<grid, kSensorThreads, smem, st>>>(a);        \
+    likelihood_field_kernel<MODE, LOGC><<<grid, kLfThreads, smem, st>>>(a);              \
+  } while (0)
+#define AMCL_LF_DISPATCH(MODE)                       \
+  do                                                 \
+  {                                                  \
+    if (logc == 4) AMCL_LF_LAUNCH(MODE, 4);          \
+    else if (logc == 2) AMCL_LF_LAUNCH(MODE, 2);     \
+    else if (logc == 0) AMCL_LF_LAUNCH(MODE, 0);     \
+    else AMCL_LF_LAUNCH(MODE, -1);                   \
   } while (0)
 
-  if (count_mode)
-  {
-    if (lut_smem) AMCL_LF_LAUNCH(MODE_COUNT, true); else AMCL_LF_LAUNCH(MODE_COUNT, false);
-  }
-  else if (model == 1)
-  {
-    if (lut_smem) AMCL_LF_LAUNCH(MODE_LF, true); else AMCL_LF_LAUNCH(MODE_LF, false);
-  }
-  else
-  {
-    if (lut_smem) AMCL_LF_LAUNCH(MODE_LFP, true); else AMCL_LF_LAUNCH(MODE_LFP, false);
-  }
+  if (count_mode) AMCL_LF_DISPATCH(MODE_COUNT);
+  else if (model == 1) AMCL_LF_DISPATCH(MODE_LF);
+  else AMCL_LF_DISPATCH(MODE_LFP);
+#undef AMCL_LF_DISPATCH
 #undef AMCL_LF_LAUNCH
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaEventRecord(c->ev_b, st));
@@ -1035,6 +1129,13 @@ static void tabulate_scan(AMCLLaserData *data, int step, bool skip_invalid, doub
   }
 }
 
+// Versions of the rank -> likelihood tables: a fresh number whenever one is rebuilt.
+static uint64_t next_lut_version()
+{
+  static uint64_t v = 0;
+  return ++v;
+}
+
 static MapCtx *ready_map(map_t *map, bool need_dist)
 {
   MapCtx *m = map_ctx(map, true);
@@ -1061,24 +1162,28 @@ double AMCLLaser::LikelihoodFieldModel(AMCLLaserData *data, pf_sample_set_t *set
   const double z_hit_denom = 2 * self->sigma_hit * self->sigma_hit;
   const double z_rand_mult = 1.0 / data->range_max;
   static std::vector<double> lut;
+  static uint64_t lut_version = 0;
   static double lut_key[7] = {0, 0, 0, 0, -1, 0, 0};
-  // dist_of_code is sqrt(code) * scale for codes 0..R^2, then max_occ_dist
+  // one entry per code rank; dist_of_code is sqrt(code) * scale for codes 0..R^2,
+  // then max_occ_dist, which is also what an off-map end point gets (:278-281)
   const double key[7] = {self->z_hit, self->z_rand, self->sigma_hit, data->range_max,
                          (double)m->R, m->scale, m->max_occ_dist};
-  if (memcmp(key, lut_key, sizeof(key)) != 0)
+  if (memcmp(key, lut_key, sizeof(key)) != 0 || lut.size() != m->code_of_rank.size())
   {
-    lut.assign(m->dist_of_code.size() + 1, 0.0);
-    for (size_t k = 0; k < lut.size(); k++)
+    lut.assign(m->code_of_rank.size(), 0.0);
+    for (size_t r = 0; r < lut.size(); r++)
     {
+      const size_t k = (size_t)m->code_of_rank[r];
       const double z = k < m->dist_of_code.size() ? m->dist_of_code[k] : m->max_occ_dist;
       double pz = 0.0;
       pz += self->z_hit * exp(-(z * z) / z_hit_denom);
       pz += self->z_rand * z_rand_mult;
-      lut[k] = pz * pz * pz;
+      lut[r] = pz * pz * pz;
     }
     memcpy(lut_key, key, sizeof(key));
+    lut_version = next_lut_version();
   }
-  return run_likelihood_field(c, which, m, 1, self->laser_pose.v, scan, lut, nullptr,
+  return run_likelihood_field(c, which, m, 1, self->laser_pose.v, scan, lut, lut_version, nullptr,
                               nullptr, nullptr);
 }
 
@@ -1100,32 +1205,35 @@ double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t 
   // likelihood_field table.
   static std::vector<double> lut;
   static std::vector<unsigned char> agree;
+  static uint64_t lut_version = 0;
   static double lut_key[8] = {0, 0, 0, 0, -1, 0, 0, 0};
   const double key[8] = {self->z_hit, self->z_rand, self->sigma_hit, data->range_max,
                          (double)m->R, m->scale, m->max_occ_dist, self->beam_skip_distance};
-  if (memcmp(key, lut_key, sizeof(key)) != 0)
+  if (memcmp(key, lut_key, sizeof(key)) != 0 || lut.size() != m->code_of_rank.size())
   {
-    lut.assign(m->dist_of_code.size() + 1, 0.0);
+    lut.assign(m->code_of_rank.size(), 0.0);
     agree.assign(((lut.size() + 1) & ~(size_t)1), 0);
-    for (size_t k = 0; k < lut.size(); k++)
+    for (size_t r = 0; r < lut.size(); r++)
     {
+      const size_t k = (size_t)m->code_of_rank[r];
       double pz = 0.0;
       if (k < m->dist_of_code.size())
       {
         const double z = m->dist_of_code[k];
-        agree[k] = z < self->beam_skip_distance ? 1 : 0;   // :419-421
+        agree[r] = z < self->beam_skip_distance ? 1 : 0;   // :419-421
         pz += self->z_hit * exp(-(z * z) / z_hit_denom);
       }
       else
         pz += self->z_hit * max_dist_prob;
       pz += self->z_rand * z_rand_mult;
-      lut[k] = log(pz);
+      lut[r] = log(pz);
     }
     memcpy(lut_key, key, sizeof(key));
+    lut_version = next_lut_version();
   }
   const bool do_beamskip = self->do_beamskip && set->converged;   // :342-344
   if (!do_beamskip)
-    return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, nullptr,
+    return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, lut_version, nullptr,
                                 nullptr, nullptr);
 
   // Beam skipping (:446-489) without the reference's N x B host scratch.  Pass 1
@@ -1139,7 +1247,7 @@ double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t 
   std::vector<int> obs_count(slots, 0), obs_mask(slots, 0);
   for (size_t k = 0; k < scan.beam_ind.size(); k++)
     if (scan.beam_ind[k] >= slots) AMCL_FATAL("beam index beyond max_beams");
-  run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, nullptr,
+  run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, lut_version, nullptr,
                        obs_count.data(), &agree);
   int skipped = 0;
   for (int b = 0; b < slots; b++)
@@ -1163,8 +1271,8 @@ double AMCLLaser::LikelihoodFieldModelProb(AMCLLaserData *data, pf_sample_set_t 
   std::vector<int> leave_out(slots, 0);
   if (!error)
     for (int b = 0; b < slots; b++) leave_out[b] = obs_mask[b] ? 0 : 1;
-  return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, leave_out.data(),
-                              nullptr, nullptr, true);
+  return run_likelihood_field(c, which, m, 2, self->laser_pose.v, scan, lut, lut_version,
+                              leave_out.data(), nullptr, nullptr, true);
 }
 
 // amcl_laser.cpp:144-213

@@ -3,7 +3,7 @@ import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from navigation_b200 import library, synth
-from tests.scenario import Side
+from navigation_b200.harness import Side
 lib = library.load()
 occ = synth.rooms_map(int(sys.argv[1]) if len(sys.argv) > 1 else 4000, seed=1)
 side = Side(lib, occ)

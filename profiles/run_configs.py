@@ -18,7 +18,7 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 from navigation_b200 import abi, library, synth  # noqa: E402
-from tests.scenario import Side  # noqa: E402
+from navigation_b200.harness import Side  # noqa: E402
 
 lib = library.load()
 lib.amclb200_set_rng(library.RNG_PHILOX, 7)
