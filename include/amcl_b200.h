@@ -101,9 +101,10 @@ void *amclb200_pf_device_samples(pf_t *pf, int set_index);
 
 /* Re-encode the distances currently held in map->cells[].occ_dist (and
  * map->max_occ_dist) into the device distance map, e.g. to evaluate the laser
- * models on the reference wavefront's output.  Aborts on values that are not
- * sqrt(integer)*scale. */
-void amclb200_map_push_distances(map_t *map);
+ * models on the reference wavefront's output.  Returns 0; or -1, with one line
+ * on stderr and the device map unchanged, when a value is not
+ * sqrt(di^2 + dj^2) * scale within the radius, or the radius exceeds 254 cells. */
+int amclb200_map_push_distances(map_t *map);
 
 /* Source index of every sample of the current set as chosen by the last
  * pf_update_resample (-1 = injected random pose); returns the count written. */

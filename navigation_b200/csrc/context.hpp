@@ -101,7 +101,7 @@ void map_finish_occupancy_on_device(MapCtx *m);  // d_occ already written on the
 void parallel_rows(int rows, const std::function<void(int, int)> &body);  // host row loops on several cores
 void map_build_distance_codes(MapCtx *m, double max_occ_dist);  // exact EDT
 void map_codes_to_host_cells(MapCtx *m);         // fills cells[].occ_dist
-void map_codes_from_host_cells(MapCtx *m);       // encodes cells[].occ_dist
+bool map_codes_from_host_cells(MapCtx *m);       // encodes cells[].occ_dist; false: a value has no code
 void map_prepare_laser_view(MapCtx *m, int reach_cells);  // (re)builds d_lf when stale or its apron is too small
 
 // ---- particle filter -------------------------------------------------------------
@@ -294,6 +294,14 @@ struct Trace
   Trace();
   void mark(const char *name);
   void report(const char *what);
+};
+
+// NVTX range around one API call (tracing).  Header-only NVTX3: a
+// no-op unless a tool (nsys, ncu --nvtx) has injected its library.
+struct ApiRange
+{
+  explicit ApiRange(const char *name);
+  ~ApiRange();
 };
 
 struct StageTimer

@@ -39,6 +39,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
+
 #define AMCLB200_EDT_STATIC_MAX_CELLS (4u * 1024u * 1024u)
 #define AMCLB200_EDT_STATIC_MAX_RADIUS 254
 #define AMCLB200_EDT_STATIC_MAX_DEVICES 64
@@ -124,9 +126,10 @@ __global__ void static_col_pass(const unsigned char *__restrict__ scratch, int s
   }
 }
 
-// Device address of the scratch array, looked up once per GPU.
-unsigned char *g_scratch_addr[AMCLB200_EDT_STATIC_MAX_DEVICES];
-bool g_scratch_ready[AMCLB200_EDT_STATIC_MAX_DEVICES];
+// Device address of the scratch array, looked up once per GPU.  Atomic: two host
+// threads may make the first call on a GPU at the same time; both then resolve
+// the same address and store it, which is harmless.
+std::atomic<unsigned char *> g_scratch_addr[AMCLB200_EDT_STATIC_MAX_DEVICES];
 
 }  // namespace
 
@@ -166,7 +169,8 @@ int amclb200_edt_codes_static(const signed char *d_occ, int size_x, int size_y, 
             err == cudaSuccess ? "device index out of range" : cudaGetErrorString(err));
     return -3;
   }
-  if (!g_scratch_ready[dev])
+  unsigned char *scratch = g_scratch_addr[dev].load(std::memory_order_acquire);
+  if (scratch == NULL)
   {
     // One-time set-up for this GPU (it is the current device): resolve the
     // array's address in THIS device's copy of the module.
@@ -178,22 +182,37 @@ int amclb200_edt_codes_static(const signed char *d_occ, int size_x, int size_y, 
                       "device %d (%s)\n", dev, cudaGetErrorString(err));
       return -3;
     }
-    g_scratch_addr[dev] = addr;
-    g_scratch_ready[dev] = true;
+    g_scratch_addr[dev].store(addr, std::memory_order_release);
+    scratch = addr;
   }
-  unsigned char *scratch = g_scratch_addr[dev];
   cudaStream_t st = (cudaStream_t)cuda_stream;
   const int R = cell_radius;
 
+  // An error left pending by earlier, unrelated work would otherwise be taken
+  // for a failure of these launches: report it as such and launch nothing.
+  err = cudaPeekAtLastError();
+  if (err != cudaSuccess)
+  {
+    fprintf(stderr, "[amcl_b200] amclb200_edt_codes_static: an earlier CUDA error is pending (%s); "
+                    "nothing launched\n", cudaGetErrorString(err));
+    return -3;
+  }
   dim3 g1((size_x + kSeg - 1) / kSeg, size_y);
   static_row_pass<<<g1, 256, kSeg + 2 * R, st>>>(d_occ, size_x, size_y, R, scratch);
+  err = cudaGetLastError();
+  if (err != cudaSuccess)
+  {
+    fprintf(stderr, "[amcl_b200] amclb200_edt_codes_static: row pass not launched (%s)\n",
+            cudaGetErrorString(err));
+    return -3;     // d_codes untouched: only the second kernel writes it
+  }
   dim3 g2((size_x + kPatch - 1) / kPatch, (size_y + kPatch - 1) / kPatch);
   const size_t smem = (size_t)(kPatch + 2 * R) * kPatch;   // <= 17.3 KB at R = 254
   static_col_pass<<<g2, 256, smem, st>>>(scratch, size_x, size_y, R, d_codes);
   err = cudaGetLastError();
   if (err != cudaSuccess)
   {
-    fprintf(stderr, "[amcl_b200] amclb200_edt_codes_static: launch failed (%s)\n",
+    fprintf(stderr, "[amcl_b200] amclb200_edt_codes_static: column pass not launched (%s)\n",
             cudaGetErrorString(err));
     return -3;
   }

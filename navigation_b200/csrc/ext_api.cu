@@ -46,11 +46,11 @@ void amclb200_map_pull_distances(map_t *map)
   map_codes_to_host_cells(m);
 }
 
-void amclb200_map_push_distances(map_t *map)
+int amclb200_map_push_distances(map_t *map)
 {
   MapCtx *m = map_ctx(map, true);
   if (!m->occ_uploaded) map_upload_occupancy(m);
-  map_codes_from_host_cells(m);
+  return map_codes_from_host_cells(m) ? 0 : -1;
 }
 
 static int copy_ints(const int *d_src, int n, int *out, int capacity)

@@ -12,6 +12,7 @@
 // IEEE sqrt and one multiply, the reference's own arithmetic (:49,:105), so it
 // equals the reference bit-for-bit wherever the reference itself is exact, and
 // is never larger.  See DESIGN.md "C1".
+#include <errno.h>
 #include <math.h>
 #include <string.h>
 
@@ -19,6 +20,8 @@
 #include <mutex>
 #include <thread>
 #include <unordered_map>
+
+#include <nvtx3/nvToolsExt.h>
 
 #include "context.hpp"
 #include "edt_rows.cuh"
@@ -83,6 +86,9 @@ void Trace::report(const char *what)
   for (auto &m : marks) cudaEventDestroy(m.second);
   marks.clear();
 }
+
+ApiRange::ApiRange(const char *name) { nvtxRangePushA(name); }
+ApiRange::~ApiRange() { nvtxRangePop(); }
 
 StageTimer::StageTimer(float *dst) : out(dst)
 {
@@ -398,14 +404,22 @@ void map_finish_occupancy_on_device(MapCtx *m)
   m->occ_uploaded = true;
 }
 
-static void set_code_table(MapCtx *m, double max_occ_dist)
+// The largest radius the uint16 codes (d2 <= 254^2, two sentinels) can hold.
+constexpr int kMaxCellRadius = 254;
+
+static int cell_radius_of(const MapCtx *m, double max_occ_dist)
 {
   // map_cspace.cpp:42 -- truncation of an fp64 quotient, e.g. 0.3/0.1 -> 2
   int R = (int)(max_occ_dist / m->scale);
-  if (R < 0) R = 0;
-  if (R > 254)
-    AMCL_FATAL("max_occ_dist/scale = %d cells exceeds the 254-cell radius the uint16 "
-               "distance codes are sized for", R);
+  return R < 0 ? 0 : R;
+}
+
+static void set_code_table(MapCtx *m, double max_occ_dist)
+{
+  const int R = cell_radius_of(m, max_occ_dist);
+  if (R > kMaxCellRadius)
+    AMCL_FATAL("max_occ_dist/scale = %d cells exceeds the %d-cell radius the uint16 "
+               "distance codes are sized for", R, kMaxCellRadius);
   m->R = R;
   m->max_occ_dist = max_occ_dist;
   m->dist_of_code.assign((size_t)R * R + 2, 0.0);
@@ -513,10 +527,6 @@ void map_build_distance_codes(MapCtx *m, double max_occ_dist)
   set_code_table(m, max_occ_dist);
   cudaStream_t st = globals().stream;
   const int R = m->R;
-  cudaEvent_t ev0, ev1;
-  AMCL_CUDA(cudaEventCreate(&ev0));
-  AMCL_CUDA(cudaEventCreate(&ev1));
-  AMCL_CUDA(cudaEventRecord(ev0, st));
   const int words = (m->sx + 63) / 64;
   const int pad = (R + 1 + 63) / 64 + 1;
   const size_t nbits = (size_t)m->sy * (words + 2 * pad);
@@ -526,6 +536,10 @@ void map_build_distance_codes(MapCtx *m, double max_occ_dist)
     m->rowbits_cap = nbits;
     AMCL_CUDA(cudaMalloc(&m->d_rowbits, nbits * sizeof(unsigned long long)));
   }
+  cudaEvent_t ev0, ev1;
+  AMCL_CUDA(cudaEventCreate(&ev0));
+  AMCL_CUDA(cudaEventCreate(&ev1));
+  AMCL_CUDA(cudaEventRecord(ev0, st));
   {
     const long long warps = (long long)m->sy * (words + 2 * pad);
     edt_pack_rows<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(m->d_occ, m->sx, m->sy, words, pad,
@@ -577,10 +591,20 @@ void map_codes_to_host_cells(MapCtx *m)
 // Inverse of the above: take whatever distances the caller wrote into
 // cells[].occ_dist (e.g. the reference wavefront's output, for like-for-like
 // sensor parity) and encode them.  Every value must be one the code table can
-// express exactly; anything else is a caller error and aborts.
-void map_codes_from_host_cells(MapCtx *m)
+// express exactly; anything else is a caller error: one line on stderr, the
+// device map is left as it was, false is returned.
+bool map_codes_from_host_cells(MapCtx *m)
 {
   map_t *map = m->host;
+  if (cell_radius_of(m, map->max_occ_dist) > kMaxCellRadius)
+  {
+    fprintf(stderr, "[amcl_b200] max_occ_dist/scale = %d cells exceeds the %d-cell radius the distance "
+                    "codes are sized for: cannot encode, device map unchanged\n",
+            cell_radius_of(m, map->max_occ_dist), kMaxCellRadius);
+    return false;
+  }
+  const double old_max = m->max_occ_dist;
+  const bool had_table = !m->dist_of_code.empty();
   set_code_table(m, map->max_occ_dist);
   const int R2 = m->R * m->R;
   size_t ncodes = (size_t)m->tiles_x * m->tiles_y * 16;
@@ -597,8 +621,12 @@ void map_codes_from_host_cells(MapCtx *m)
         double q = d / m->scale;
         long d2 = lround(q * q);
         if (d2 < 0 || d2 > R2 || m->dist_of_code[d2] != d || m->rank_of_code[d2] == 0xffff)
-          AMCL_FATAL("occ_dist %.17g at cell (%d,%d) is not sqrt(d2)*scale for an integer "
-                     "d2 <= %d; cannot encode", d, i, j, R2);
+        {
+          fprintf(stderr, "[amcl_b200] occ_dist %.17g at cell (%d,%d) is not sqrt(di^2 + dj^2)*scale "
+                          "with di^2 + dj^2 <= %d: cannot encode, device map unchanged\n", d, i, j, R2);
+          if (had_table) set_code_table(m, old_max);   // the codes on the device still mean what they meant
+          return false;
+        }
         code = (int)d2;
       }
       codes[((size_t)(j >> 2) * m->tiles_x + (i >> 2)) * 16 + (j & 3) * 4 + (i & 3)] =
@@ -609,6 +637,7 @@ void map_codes_from_host_cells(MapCtx *m)
   AMCL_CUDA(cudaStreamSynchronize(globals().stream));
   m->dist_valid = true;
   m->generation++;
+  return true;
 }
 
 }  // namespace amclb200
@@ -652,21 +681,77 @@ map_cell_t *map_get_cell(map_t *map, double ox, double oy, double oa)
   return map->cells + MAP_INDEX(map, i, j);
 }
 
-// map_store.c:41 loads a PGM from disk; the node never calls it (it converts a
-// ROS message itself) and file I/O is outside the path.  Exported so that
-// anything linking the symbol still links; reports failure.
+// map_store.c:39-136: fills the grid from a binary PGM ("P5") file.  Host code;
+// the occupancy reaches the device with the next map_update_cspace().  Rules of
+// the reference: '#' comment lines may follow the magic number; the first image
+// row is the TOP row of the map (j = height - 1); a pixel below depth/4 is
+// occupied, above 3*depth/4 free, anything between unknown (the other way round
+// with `negate`); a map that already has cells must have the file's dimensions;
+// a short file leaves fgetc()'s EOF (-1) as the pixel value, as there.
 int map_load_occ(map_t *map, const char *filename, double scale, int negate)
 {
-  (void)map; (void)scale; (void)negate;
-  fprintf(stderr, "[amcl_b200] map_load_occ(%s): PGM loading is out of scope; fill map_t "
-                  "yourself as amcl_node's convertMap does\n", filename ? filename : "");
-  return -1;
+  FILE *file = fopen(filename, "r");
+  if (file == NULL)
+  {
+    fprintf(stderr, "%s: %s\n", strerror(errno), filename);
+    return -1;
+  }
+  char magic[3] = {0, 0, 0};
+  if (fscanf(file, "%2s \n", magic) != 1 || strcmp(magic, "P5") != 0)
+  {
+    fprintf(stderr, "incorrect image format; must be PGM/binary");
+    fclose(file);
+    return -1;
+  }
+  int ch;
+  while ((ch = fgetc(file)) == '#')
+    while ((ch = fgetc(file)) != '\n' && ch != EOF) {}
+  ungetc(ch, file);
+  int width = 0, height = 0, depth = 0;
+  if (fscanf(file, " %d %d \n %d \n", &width, &height, &depth) != 3 || width <= 0 || height <= 0)
+  {
+    fprintf(stderr, "Failed ot read image dimensions");
+    fclose(file);
+    return -1;
+  }
+  if (map->cells == NULL)
+  {
+    map->scale = scale;
+    map->size_x = width;
+    map->size_y = height;
+    map->cells = (map_cell_t *)calloc((size_t)width * height, sizeof(map->cells[0]));
+  }
+  else if (width != map->size_x || height != map->size_y)
+  {
+    fclose(file);
+    return -1;
+  }
+  const int lo = depth / 4, hi = 3 * depth / 4;
+  for (int j = height - 1; j >= 0; j--)
+    for (int i = 0; i < width; i++)
+    {
+      ch = fgetc(file);
+      const int dark = ch < lo, light = ch > hi;
+      const int occ = dark ? (negate ? -1 : +1) : (light ? (negate ? +1 : -1) : 0);
+      if (!MAP_VALID(map, i, j)) continue;
+      map->cells[MAP_INDEX(map, i, j)].occ_state = occ;
+    }
+  fclose(file);
+  // a device copy made from earlier contents of these cells is stale now
+  MapCtx *m = map_ctx(map, false);
+  if (m)
+  {
+    m->occ_uploaded = false;
+    m->dist_valid = false;
+  }
+  return 0;
 }
 
 // map_cspace.cpp:120-176.  Uploads the occupancy states, runs the exact EDT on
 // the device and writes occ_dist back into the caller's cells.
 void map_update_cspace(map_t *map, double max_occ_dist)
 {
+  ApiRange range("amcl_b200:map_update_cspace");
   MapCtx *m = map_ctx(map, true);
   // amclb200_map_set_mirror(map, 0): the device copy is authoritative -- the
   // caller's cells are read once (or never, after amclb200_map_from_image) and

@@ -291,6 +291,7 @@ void pf_free(pf_t *pf)
 // pf.c:136-174
 void pf_init(pf_t *pf, pf_vector_t mean, pf_matrix_t cov)
 {
+  ApiRange range("amcl_b200:pf_init");
   PfCtx *c = pf_ctx(pf);
   const int which = pf->current_set;
   pf_sample_set_t *set = pf->sets + which;
@@ -371,6 +372,7 @@ void pf_update_action(pf_t *pf, pf_action_model_fn_t action_fn, void *action_dat
 // pf.c:268-318
 void pf_update_sensor(pf_t *pf, pf_sensor_model_fn_t sensor_fn, void *sensor_data)
 {
+  ApiRange range("amcl_b200:pf_update_sensor");
   PfCtx *c = pf_ctx(pf);
   const int which = pf->current_set;
   pf_sample_set_t *set = pf->sets + which;
@@ -391,6 +393,7 @@ void pf_update_sensor(pf_t *pf, pf_sensor_model_fn_t sensor_fn, void *sensor_dat
 // pf.c:363-510
 void pf_update_resample(pf_t *pf)
 {
+  ApiRange range("amcl_b200:pf_update_resample");
   PfCtx *c = pf_ctx(pf);
   StageTimer timer(&c->ms_resample);
   run_resample(c);

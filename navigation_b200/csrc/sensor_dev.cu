@@ -104,20 +104,21 @@ enum { MODE_LF = 0, MODE_LFP = 1, MODE_COUNT = 2 };
 
 constexpr int kSensorThreads = 256;     // beam model
 #ifndef AMCL_LF_THREADS
-#define AMCL_LF_THREADS 384
+#define AMCL_LF_THREADS 512
 #endif
 #ifndef AMCL_LF_MINBLOCKS
-#define AMCL_LF_MINBLOCKS 2
+#define AMCL_LF_MINBLOCKS 1
 #endif
-constexpr int kLfThreads = AMCL_LF_THREADS;   // likelihood-field kernels: 2 CTAs of 12 warps per SM
+constexpr int kLfThreads = AMCL_LF_THREADS;   // likelihood-field kernels: one CTA of 16 warps per SM (~126 registers)
 constexpr double kCellGuard = 536870912.0;  // 2^29: beyond this nothing is on a map
 
 // Particles handled together by one warp: every beam-table entry fetched from
 // shared memory is applied to kBlockP particles, which divides the shared-
 // memory traffic of the table by kBlockP and keeps kBlockP independent map
-// gathers in flight per lane.
+// gathers in flight per lane.  Measured at 16 Mi x 1059 (profiles/r2_lf_kernel.md):
+// 8 particles x 16 warps per SM 15.5 ms, 4 x 24 warps 16.1 ms, 16 x 8 warps 17.9 ms.
 #ifndef AMCL_LF_BLOCKP
-#define AMCL_LF_BLOCKP 4
+#define AMCL_LF_BLOCKP 8
 #endif
 constexpr int kBlockP = AMCL_LF_BLOCKP;
 

@@ -55,7 +55,8 @@ class Side:
         d = np.ascontiguousarray(dist, dtype=np.float64)
         self.lib.amcl_c_map_set_occ_dist(self.map, d.ctypes.data, max_occ_dist)
         if self.is_gpu:
-            self.lib.amclb200_map_push_distances(self.map)
+            rc = self.lib.amclb200_map_push_distances(self.map)
+            assert rc == 0, "occ_dist values the device codes cannot express"
 
     # -- filter ------------------------------------------------------------------
     def alloc(self, min_samples, max_samples, alpha_slow=0.0, alpha_fast=0.0,

@@ -28,7 +28,7 @@ EXTENSION_SYMBOLS = {
     "amclb200_pf_pull_samples": (None, [abi.pf_p]),
     "amclb200_pf_push_samples": (None, [abi.pf_p]),
     "amclb200_pf_device_samples": (C.c_void_p, [abi.pf_p, C.c_int]),
-    "amclb200_map_push_distances": (None, [abi.map_p]),
+    "amclb200_map_push_distances": (C.c_int, [abi.map_p]),
     "amclb200_pf_resample_sources": (C.c_int, [abi.pf_p, C.c_void_p, C.c_int]),
     "amclb200_pf_cluster_labels": (C.c_int, [abi.pf_p, C.c_void_p, C.c_int]),
     "amclb200_pf_cumulative_table": (C.c_int, [abi.pf_p, C.c_void_p, C.c_int]),

@@ -135,6 +135,7 @@ int main()
   ok = copy->UpdateSensor(pf, (AMCLSensorData *)&ldata) && ok;
   dump("lf", pf);
   laser->SetModelBeam(0.95, 0.1, 0.05, 0.05, 0.2, 0.1, 0.0);
+  laser->SetLaserPose(lp);                      // the constructor leaves laser_pose unset
   ldata.sensor = laser;
   ok = laser->UpdateSensor(pf, (AMCLSensorData *)&ldata) && ok;
   dump("beam", pf);

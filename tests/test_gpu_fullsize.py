@@ -159,3 +159,21 @@ def test_pf_init_matches_reference_bit_exact(lib, ref):
     assert ca == cb and ka == kb
     assert np.allclose(ma, mb, rtol=1e-9, atol=1e-12)
     assert np.allclose(va, vb, rtol=1e-7, atol=1e-12)
+
+
+def test_push_distances_reports_values_without_a_code(lib):
+    """amclb200_map_push_distances: a distance that is not sqrt(di^2 + dj^2) * scale
+    is the caller's error -- -1 and the device map as it was, not an abort."""
+    occ = synth.rooms_map(120, seed=1, room=40, door=(10, 20))
+    side = Side(lib, occ)
+    side.update_cspace(1.0)
+    good = side.occ_dist()
+    bad = good.copy()
+    bad[17, 23] = 0.123                          # not a cell distance
+    lib.amcl_c_map_set_occ_dist(side.map, np.ascontiguousarray(bad).ctypes.data, 1.0)
+    assert lib.amclb200_map_push_distances(side.map) == -1
+    lib.amcl_c_map_set_occ_dist(side.map, np.ascontiguousarray(np.sqrt(7.0) * 0.05 + 0 * good).ctypes.data, 1.0)
+    assert lib.amclb200_map_push_distances(side.map) == -1      # 7 is not a sum of two squares
+    lib.amclb200_map_pull_distances(side.map)                    # the device map still holds the transform
+    assert np.array_equal(side.occ_dist(), good)
+    side.close()

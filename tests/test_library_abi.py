@@ -156,3 +156,71 @@ def test_same_probes_compile_against_reference_headers():
             out = subprocess.run(["g++", "-c", path, "-o", os.path.join(d, "p.o")] + ref_inc + flags,
                                  capture_output=True, text=True)
             assert out.returncode == 0, out.stderr
+
+
+# ---- map_load_occ (map_store.c:39-136): host code, compared with the compiled reference ----
+
+def _write_pgm(path, pixels, depth, comment=True):
+    h, w = pixels.shape
+    with open(path, "wb") as f:
+        f.write(b"P5\n")
+        if comment:
+            f.write(b"# made by tests/test_library_abi.py\n# second comment line\n")
+        f.write(b"%d %d\n%d\n" % (w, h, depth))
+        f.write(pixels.astype("uint8").tobytes())
+
+
+def _load_states(lib, path, scale, negate, prealloc=None):
+    import numpy as np
+
+    lib.map_alloc.restype = abi.map_p
+    lib.map_load_occ.argtypes = [abi.map_p, C.c_char_p, C.c_double, C.c_int]
+    lib.map_load_occ.restype = C.c_int
+    lib.map_free.argtypes = [abi.map_p]
+    m = lib.map_alloc()
+    if prealloc is not None:
+        libc = C.CDLL(None)
+        libc.calloc.restype = C.c_void_p
+        libc.calloc.argtypes = [C.c_size_t, C.c_size_t]
+        m.contents.size_x, m.contents.size_y = prealloc
+        m.contents.cells = C.cast(libc.calloc(prealloc[0] * prealloc[1], 16), C.POINTER(abi.map_cell_t))
+    rc = lib.map_load_occ(m, path.encode(), scale, negate)
+    out = None
+    if rc == 0:
+        sx, sy = m.contents.size_x, m.contents.size_y
+        raw = np.ctypeslib.as_array(C.cast(m.contents.cells, C.POINTER(C.c_int32)), shape=(sy, sx, 4))
+        out = (raw[:, :, 0].copy(), sx, sy, m.contents.scale)
+    lib.map_free(m)
+    return rc, out
+
+
+@pytest.mark.parametrize("depth,negate", [(255, 0), (255, 1), (100, 0), (15, 1)])
+def test_map_load_occ_matches_reference(so, ref, tmp_path, depth, negate):
+    import numpy as np
+
+    rng = np.random.default_rng(depth + negate)
+    px = rng.integers(0, depth + 1, size=(37, 53))
+    px[0, :] = 0                     # top image row = last map row
+    px[:, 0] = depth
+    path = str(tmp_path / "m.pgm")
+    _write_pgm(path, px, depth)
+    rc_a, a = _load_states(ref, path, 0.05, negate)
+    rc_b, b = _load_states(so, path, 0.05, negate)
+    assert rc_a == rc_b == 0
+    assert a[1:] == b[1:] == (53, 37, 0.05)
+    assert np.array_equal(a[0], b[0])
+    assert set(np.unique(b[0]).tolist()) <= {-1, 0, 1}
+    # a map that already has cells must match the file's size (map_store.c:85-92)
+    assert _load_states(ref, path, 0.05, negate, prealloc=(53, 36))[0] == -1
+    assert _load_states(so, path, 0.05, negate, prealloc=(53, 36))[0] == -1
+    rc_c, c = _load_states(so, path, 0.05, negate, prealloc=(53, 37))
+    assert rc_c == 0 and np.array_equal(c[0], a[0])
+
+
+def test_map_load_occ_rejects_what_the_reference_rejects(so, ref, tmp_path):
+    bad = str(tmp_path / "bad.pgm")
+    with open(bad, "wb") as f:
+        f.write(b"P2\n2 2\n255\n0 0 0 0\n")
+    for lib in (ref, so):
+        assert _load_states(lib, bad, 0.05, 0)[0] == -1
+        assert _load_states(lib, str(tmp_path / "missing.pgm"), 0.05, 0)[0] == -1

@@ -24,15 +24,21 @@ from tests.scenario import Side
 pytestmark = pytest.mark.gpu
 
 
-def _static_distances(lib, torch, occ, scale, max_d):
+def _static_codes(lib, torch, occ, R, stream=None):
     sy, sx = occ.shape
-    R = int(max_d / scale)                       # map_cspace.cpp:42
     d_occ = torch.from_numpy(occ).cuda()         # caller-owned input
     d_codes = torch.full((sy, sx), -1, dtype=torch.int16, device="cuda")   # caller-owned output
-    rc = lib.amclb200_edt_codes_static(d_occ.data_ptr(), sx, sy, R, d_codes.data_ptr(), None)
+    torch.cuda.synchronize()
+    rc = lib.amclb200_edt_codes_static(d_occ.data_ptr(), sx, sy, R, d_codes.data_ptr(),
+                                       C.c_void_p(stream.cuda_stream) if stream is not None else None)
     assert rc == 0
     torch.cuda.synchronize()
-    codes = d_codes.cpu().numpy().view(np.uint16).astype(np.int64)
+    return d_codes.cpu().numpy().view(np.uint16).astype(np.int64)
+
+
+def _static_distances(lib, torch, occ, scale, max_d):
+    R = int(max_d / scale)                       # map_cspace.cpp:42
+    codes = _static_codes(lib, torch, occ, R)
     dist = np.sqrt(codes.astype(np.float64)) * scale
     dist[codes > R * R] = max_d
     return dist
@@ -57,6 +63,39 @@ def test_static_edt_matches_map_update_cspace_twice_in_a_row(gpu_lib):
         got = _static_distances(lib, torch, occ, scale, max_d)
         want = _reference_entry_distances(lib, occ, scale, max_d)
         assert np.array_equal(got, want)
+
+
+def test_static_edt_against_the_oracle_and_without_allocating(gpu_lib, port):
+    """Directly against the CPU oracle's exact transform (not only against the other
+    CUDA entry point), on shapes that cross the row pass's 512-cell segments, at
+    the largest and the smallest radius, on a width that is no multiple of 32 and
+    on a caller's own stream; and the property the entry point exists for: the
+    free device memory the driver reports is the same before and after a call."""
+    import torch
+
+    from oracle import oracle
+
+    lib = gpu_lib
+    wide = np.ascontiguousarray(synth.rooms_map(1100, seed=21, room=90, door=(30, 50), clutter_mod=700)[:70])
+    odd = np.ascontiguousarray(synth.rooms_map(600, seed=22, room=70, door=(20, 40), clutter_mod=500)[:333, :557])
+    cases = [(wide, 254, None), (wide, 0, None), (odd, 40, None), (odd, 17, torch.cuda.Stream())]
+    _static_codes(lib, torch, odd, 3)            # set-up call for this GPU, outside the measurement
+    for occ, R, stream in cases:
+        d2 = oracle.edt_exact(occ, R).astype(np.int64)
+        want = np.where((d2 < 0) | (d2 > R * R), R * R + 1, d2)    # the oracle marks "beyond R" with -1
+        sy, sx = occ.shape
+        d_occ = torch.from_numpy(occ).cuda()
+        d_codes = torch.full((sy, sx), -1, dtype=torch.int16, device="cuda")
+        torch.cuda.synchronize()
+        free_before, _ = torch.cuda.mem_get_info()
+        rc = lib.amclb200_edt_codes_static(d_occ.data_ptr(), sx, sy, R, d_codes.data_ptr(),
+                                           C.c_void_p(stream.cuda_stream) if stream is not None else None)
+        torch.cuda.synchronize()
+        free_after, _ = torch.cuda.mem_get_info()
+        assert rc == 0
+        assert free_after == free_before         # cudaMemGetInfo: nothing was allocated or freed
+        got = d_codes.cpu().numpy().view(np.uint16).astype(np.int64)
+        assert np.array_equal(got, want), (occ.shape, R)
 
 
 def test_static_edt_refuses_maps_beyond_its_scratch(gpu_lib):
