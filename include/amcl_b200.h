@@ -207,6 +207,15 @@ typedef void (*amclb200_allgather_fn)(void *d_buf, unsigned long long bytes_per_
  * keys before resampling, per-cluster sums).  Results equal the one-GPU run. */
 void amclb200_pf_set_shard(pf_t *pf, int rank, int world, amclb200_allreduce_fn allreduce,
                            amclb200_allgather_fn allgather, void *user);
+/* The same, with the exchanges on an NCCL communicator the LIBRARY owns: no
+ * callbacks, the collectives are enqueued on the library's stream from C++ (this
+ * is the path bench.py uses on GPUs; the callback form stays for programs that
+ * bring their own transport, e.g. gloo on host buffers).  Rank 0 obtains an id
+ * with amclb200_nccl_unique_id (128 bytes, an ncclUniqueId) and distributes it
+ * by any host-side means; then every rank calls amclb200_pf_set_shard_nccl
+ * (collective).  libnccl.so.2 is opened on first use only.  Returns 0 / -1. */
+int amclb200_nccl_unique_id(unsigned char out[128]);
+void amclb200_pf_set_shard_nccl(pf_t *pf, int rank, int world, const unsigned char id[128]);
 /* Collective, optional, once after amclb200_pf_set_shard: map every rank's particle
  * arrays into this process (CUDA IPC).  pf_update_resample then all-gathers only
  * the 8-byte weights and reads the poses it picks from their owners' memory over

@@ -126,15 +126,29 @@ enum { SHARD_SUM = 0, SHARD_MIN = 1, SHARD_MAX = 2 };
 struct Shard
 {
   int rank = 0, world = 1;
-  shard_allreduce_fn allreduce = nullptr;
-  shard_allgather_fn allgather = nullptr;
+  // Either the host program's callbacks (amclb200_pf_set_shard: torch.distributed
+  // in Python programs, gloo on host buffers in the CPU tests) ...
+  shard_allreduce_fn cb_allreduce = nullptr;
+  shard_allgather_fn cb_allgather = nullptr;
   void *user = nullptr;
+  // ... or an NCCL communicator the library owns (amclb200_pf_set_shard_nccl,
+  // shard_nccl.cu): collectives are enqueued on the library's stream straight
+  // from C++, no host round trip through the caller.
+  void *nccl_comm = nullptr;
   bool on() const { return world > 1; }
   int chunk(int n) const { return (n + world - 1) / world; }
   int lo(int n) const { int v = rank * chunk(n); return v < n ? v : n; }
   int hi(int n) const { int v = (rank + 1) * chunk(n); return v < n ? v : n; }
   int count(int n) const { return hi(n) - lo(n); }
+  // same call shape as the callbacks (the last argument is ignored)
+  void allreduce(void *d_buf, int count, int dtype, int op, void * = nullptr) const;
+  void allgather(void *d_buf, unsigned long long bytes_per_rank, void * = nullptr) const;
 };
+
+// shard_nccl.cu
+void nccl_allreduce(void *comm, void *d_buf, int count, int dtype, int op);
+void nccl_allgather(void *comm, int rank, void *d_buf, unsigned long long bytes_per_rank);
+void nccl_release(void *comm);
 
 struct PfCtx
 {

@@ -106,6 +106,7 @@ void pf_ctx_release(pf_t *pf)
   for (void *p : c->peer_opened) cudaIpcCloseMemHandle(p);
   for (int j = 0; j < 2; j++) if (c->d_peer_tab[j]) cudaFree((void *)c->d_peer_tab[j]);
   if (c->d_wpack) cudaFree(c->d_wpack);
+  if (c->shard.nccl_comm) nccl_release(c->shard.nccl_comm);
   cudaFree(c->d_cum); cudaFree(c->d_draws); cudaFree(c->d_src); cudaFree(c->d_label);
   cudaFree(c->d_keys); cudaFree(c->d_slot); cudaFree(c->d_flag); cudaFree(c->d_scan);
   cudaFree(c->d_scan_tiles); cudaFree(c->d_tab_key); cudaFree(c->d_tab_first); cudaFree(c->d_tab_aux); cudaFree(c->d_scalars); cudaFree(c->d_ints);

@@ -38,6 +38,8 @@ EXTENSION_SYMBOLS = {
     "amclb200_pf_load_device": (None, [abi.pf_p, C.c_void_p, C.c_int]),
     "amclb200_pf_set_shard": (None, [abi.pf_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "amclb200_pf_enable_peer_access": (None, [abi.pf_p]),
+    "amclb200_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "amclb200_pf_set_shard_nccl": (None, [abi.pf_p, C.c_int, C.c_int, C.c_void_p]),
     "amclb200_pf_load_device_shard": (None, [abi.pf_p, C.c_void_p, C.c_int]),
     "amclb200_pf_shard_range": (None, [abi.pf_p, C.c_int, C.POINTER(C.c_int)]),
     "amclb200_launch_count": (C.c_uint64, []),

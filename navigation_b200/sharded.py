@@ -97,6 +97,22 @@ class Collectives:
     def allgather(self, ptr, bytes_per_rank):
         self._allgather(ptr, bytes_per_rank, None)
 
+    def attach_nccl(self, lib, pf, peer_access=True):
+        """The same, with the exchanges on an NCCL communicator owned by the library
+        (amclb200_pf_set_shard_nccl): this object only distributes the 128-byte
+        ncclUniqueId; no collective of the filter passes through Python after that."""
+        assert self.on_gpu, "the library's own NCCL path needs device buffers"
+        ident = (C.c_ubyte * 128)()
+        if self.rank == 0:
+            assert lib.amclb200_nccl_unique_id(ident) == 0
+        t = torch.tensor(list(ident), dtype=torch.uint8, device=self.device)
+        dist.broadcast(t, src=0, group=self.group)
+        ident = (C.c_ubyte * 128)(*t.cpu().tolist())
+        lib.amclb200_pf_set_shard_nccl(pf, self.rank, self.world, ident)
+        self.calls["in_library_nccl"] = True
+        if peer_access and self.world > 1:
+            lib.amclb200_pf_enable_peer_access(pf)
+
     def attach(self, lib, pf, peer_access=True):
         """Make `pf` this rank's shard of a world-wide filter.  With peer_access
         (GPU only) every rank's particle arrays are mapped into every process, so
