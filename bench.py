@@ -62,6 +62,9 @@ def parse():
     ap.add_argument("--cpu-workers", type=int, default=0, help="0 = one per host core (max 32)")
     ap.add_argument("--cpu-steps", type=int, default=3, help="timed steps of a CPU reference leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--collectives", default="nccl", choices=["nccl", "torch"],
+                    help="multi-GPU exchanges: the library's own NCCL communicator (default) or "
+                         "torch.distributed callbacks")
     ap.add_argument("--parity-particles", type=int, default=1 << 20,
                     help="particles of the oracle parity pass run before the timed loop; 0 = skip")
     return ap.parse_args()
@@ -503,7 +506,10 @@ def b200_arm(args):
     if world > 1:
         from navigation_b200 import sharded
         coll = sharded.Collectives(device=torch.device("cuda", local))
-        coll.attach(lib, side.pf)
+        if args.collectives == "nccl":
+            coll.attach_nccl(lib, side.pf)
+        else:
+            coll.attach(lib, side.pf)
     rng2 = (C.c_int * 2)()
     lib.amclb200_pf_shard_range(side.pf, n_total, rng2)
     own_lo, own_hi = rng2[0], rng2[1]

@@ -335,9 +335,10 @@ struct PickArgs
   const Particle *src;
   int n_src;
   const double *cum;        // n_src + 1 entries
-  const double *draws;      // (u_test, r) per candidate
+  const double *draws;      // (u_test, r) per candidate; null: drawn here from the Philox stream
+  unsigned long long philox_key;
   const Particle *injected; // random poses for candidates flagged on the host, or null
-  const int *inject_slot;   // candidate -> index into injected, -1 otherwise; or null
+  const int *inject_slot;   // candidate -> 1 + index into injected, 0 otherwise; or null
   Particle *dst;
   int *src_index;
   unsigned long long *keys;
@@ -362,11 +363,21 @@ __global__ void pick_and_copy(const PickArgs a)
   const int m = a.first + t;
   Particle s;
   int from = -1;
-  if (a.inject_slot && a.inject_slot[m] >= 0)
-    s = load_particle(a.injected + a.inject_slot[m]);
+  if (a.inject_slot && a.inject_slot[m] > 0)      // slot + 1; 0 = not injected
+    s = load_particle(a.injected + (a.inject_slot[m] - 1));
   else
   {
-    const double r = a.draws[2 * (size_t)m + 1];
+    double r;
+    if (a.draws)
+      r = a.draws[2 * (size_t)m + 1];
+    else
+    {
+      // the same two uniforms philox_resample_draws would have stored: the first is
+      // the recovery test (pf.c:430), unused here because w_diff == 0
+      PhiloxStream rng(a.philox_key, (uint64_t)m);
+      (void)rng.uniform();
+      r = rng.uniform();
+    }
     int lo;
     if (a.bucket_index)
     {
@@ -513,12 +524,15 @@ __global__ void bin_lookup(const Particle *__restrict__ set, int base, int n, co
   {
     int kx, ky, kt;
     unpack_key(key, &kx, &ky, &kt);
-    slot_of[m] = (unsigned int)(((kt - T.t0) * T.ey + (ky - T.y0)) * T.ex + (kx - T.x0));
+    const int dx = kx - T.x0, dy = ky - T.y0, dt = kt - T.t0;
+    // a pose outside the grid cannot have been entered into it: no slot
+    const bool inside = dx >= 0 && dx < T.ex && dy >= 0 && dy < T.ey && dt >= 0 && dt < T.et;
+    slot_of[m] = inside ? (unsigned int)((dt * T.ey + dy) * T.ex + dx) : 0xFFFFFFFFu;
     return;
   }
   unsigned int h = hash_key(key) & T.mask;
   while (T.key[h] != key && T.key[h] != kEmptyKey) h = (h + 1) & T.mask;
-  slot_of[m] = h;
+  slot_of[m] = T.key[h] == key ? h : 0xFFFFFFFFu;
 }
 
 __global__ void mark_first(const unsigned int *__restrict__ first, const unsigned int *__restrict__ slot_of,
@@ -963,8 +977,11 @@ __global__ void cluster_accumulate(const Particle *__restrict__ set, int n,
     if (live)
     {
       const Particle s = load_particle(set + i);
-      const unsigned int root = root_of_slot[slot_of[i]];
-      label = cid_of_root[root];
+      // (a sample without a slot or in a bin nobody entered gets no label and is
+      // left out of the sums; cannot happen while every rank sees the same poses)
+      const unsigned int slot = slot_of[i];
+      const unsigned int root = slot != 0xFFFFFFFFu ? root_of_slot[slot] : 0xFFFFFFFFu;
+      label = root != 0xFFFFFFFFu ? cid_of_root[root] : 0xFFFFFFFFu;
       double sn, cs;
       sincos(s.th, &sn, &cs);
       v[0] = 1.0;
@@ -1555,6 +1572,8 @@ void run_resample(PfCtx *c)
   std::vector<Particle> injected;
   unsigned short saved_state[3] = {0, 0, 0};
   const bool host_stream = globals().rng == RNG_DRAND48;
+  uint64_t philox_key = 0;
+  bool draws_in_kernel = false;
   if (host_stream)
   {
     // Draw exactly as pf.c:426-460 would for a full run to max_samples, then
@@ -1586,11 +1605,14 @@ void run_resample(PfCtx *c)
   }
   else
   {
-    const uint64_t key = globals().philox_seed ^ (0xA0761D6478BD642Full * (++c->step));
-    philox_resample_draws<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_draws, maxs, key);
-    AMCL_LAUNCH_CHECK();
+    philox_key = globals().philox_seed ^ (0xA0761D6478BD642Full * (++c->step));
+    // without recovery injection nobody but the pick kernel needs the draws: it
+    // regenerates them from (key, sample index) instead of reading 16 B per sample
+    draws_in_kernel = !(w_diff > 0.0);
     if (w_diff > 0.0)
     {
+      philox_resample_draws<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_draws, maxs, philox_key);
+      AMCL_LAUNCH_CHECK();
       // recovery path: candidates with u < w_diff take a host-generated pose
       std::vector<double> draws((size_t)2 * maxs);
       AMCL_CUDA(cudaMemcpyAsync(draws.data(), c->d_draws, sizeof(double) * 2 * (size_t)maxs,
@@ -1608,16 +1630,56 @@ void run_resample(PfCtx *c)
     }
   }
 
+  // Sharded: what the HOST contributed must be the same on every rank -- the
+  // caller's random_pose_fn draws from each process's own libc stream, and in
+  // drand48 mode so do the uniforms.  Rank 0's version wins: the others zero
+  // their copy and a SUM all-reduce hands it round (x + 0 is exact).
+  int n_injected = (int)injected.size();
+  if (sh.on() && (host_stream || w_diff > 0.0))
+  {
+    c->h_ints[I_MOVED] = sh.rank == 0 ? n_injected : 0;
+    AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_MOVED, c->h_ints + I_MOVED, sizeof(int), cudaMemcpyHostToDevice, st));
+    sh.allreduce(c->d_ints + I_MOVED, 1, SHARD_I32, SHARD_SUM, sh.user);
+    sync_ints(c, I_MOVED, 1);
+    n_injected = c->h_ints[I_MOVED];
+    if (host_stream)
+    {
+      if (sh.rank != 0) AMCL_CUDA(cudaMemsetAsync(c->d_draws, 0, sizeof(double) * 2 * (size_t)maxs, st));
+      for (size_t off = 0; off < 2 * (size_t)maxs; off += (size_t)1 << 28)   // int-sized pieces
+      {
+        const size_t len = 2 * (size_t)maxs - off < ((size_t)1 << 28) ? 2 * (size_t)maxs - off : (size_t)1 << 28;
+        sh.allreduce(c->d_draws + off, (int)len, SHARD_F64, SHARD_SUM, sh.user);
+      }
+    }
+  }
   Particle *d_injected = nullptr;
   int *d_inject_slot = nullptr;
-  if (!injected.empty())
+  if (n_injected > 0)
   {
-    AMCL_CUDA(cudaMalloc(&d_injected, sizeof(Particle) * injected.size()));
+    const bool mine = !sh.on() || sh.rank == 0;
+    if (inject_slot.empty()) inject_slot.assign(maxs, -1);
+    injected.resize((size_t)n_injected);
+    AMCL_CUDA(cudaMalloc(&d_injected, sizeof(Particle) * (size_t)n_injected));
     AMCL_CUDA(cudaMalloc(&d_inject_slot, sizeof(int) * (size_t)maxs));
-    AMCL_CUDA(cudaMemcpyAsync(d_injected, injected.data(), sizeof(Particle) * injected.size(),
-                              cudaMemcpyHostToDevice, st));
-    AMCL_CUDA(cudaMemcpyAsync(d_inject_slot, inject_slot.data(), sizeof(int) * (size_t)maxs,
-                              cudaMemcpyHostToDevice, st));
+    if (mine)
+    {
+      // slots travel as slot + 1 so that "none" is 0, the neutral element of the sum
+      for (int m = 0; m < maxs; m++) inject_slot[m] += 1;
+      AMCL_CUDA(cudaMemcpyAsync(d_injected, injected.data(), sizeof(Particle) * (size_t)n_injected,
+                                cudaMemcpyHostToDevice, st));
+      AMCL_CUDA(cudaMemcpyAsync(d_inject_slot, inject_slot.data(), sizeof(int) * (size_t)maxs,
+                                cudaMemcpyHostToDevice, st));
+    }
+    else
+    {
+      AMCL_CUDA(cudaMemsetAsync(d_injected, 0, sizeof(Particle) * (size_t)n_injected, st));
+      AMCL_CUDA(cudaMemsetAsync(d_inject_slot, 0, sizeof(int) * (size_t)maxs, st));
+    }
+    if (sh.on())
+    {
+      sh.allreduce(d_injected, 4 * n_injected, SHARD_F64, SHARD_SUM, sh.user);
+      sh.allreduce(d_inject_slot, maxs, SHARD_I32, SHARD_SUM, sh.user);
+    }
   }
 
   // ---- pick sources, copy poses, bin keys -----------------------------------
@@ -1655,7 +1717,8 @@ void run_resample(PfCtx *c)
     pa.bucket_index = c->d_bucket_index;
     pa.buckets = buckets;
   }
-  pa.draws = c->d_draws;
+  pa.draws = draws_in_kernel ? nullptr : c->d_draws;
+  pa.philox_key = philox_key;
   pa.injected = d_injected;
   pa.inject_slot = d_inject_slot;
   pa.dst = c->d_set[ib];

@@ -40,9 +40,16 @@ def main():
     for mode in ("single", "sharded"):
         lib.amclb200_set_rng(library.RNG_PHILOX, 0xC0FFEE)
         side = Side(lib, occ)
-        side.alloc(100, n, pop_err=0.01, pop_z=0.99)
+        model = os.environ.get("SHARD_MODEL", "lf")       # lf | lfp | lfp_skip | beam | lf_recover
+        recover = model == "lf_recover"
+        if recover:
+            # recovery injection (pf.c:411-431): a share of the new samples are fresh
+            # poses from the caller's host callback; tight cloud, so the KLD bound cuts
+            side.alloc(100, n, alpha_slow=0.001, alpha_fast=0.1, pop_err=0.01, pop_z=0.99)
+            model = "lf"
+        else:
+            side.alloc(100, n, pop_err=0.01, pop_z=0.99)
         lib.amclb200_set_mirror(side.pf, 0)
-        model = os.environ.get("SHARD_MODEL", "lf")       # lf | lfp | lfp_skip | beam
         if model == "lfp_skip":
             side.make_laser(beams, model="lfp", beamskip=(1, 0.5, 0.3, 0.9))
         else:
@@ -60,8 +67,15 @@ def main():
             # beam skipping needs a converged set (amcl_laser.cpp:342): a tight cloud
             cloud = synth.gaussian_cloud(pose, (0.05, 0.05, 0.05), n, 5)
             cloud[:, 3] = 1.0 / n
+        if recover:
+            cloud = synth.gaussian_cloud(pose, (0.3, 0.3, 0.1), n, 5)
+            cloud[:, 3] = 1.0 / n
         if mode == "sharded":
-            coll.attach(lib, side.pf, peer_access=os.environ.get("SHARD_P2P", "1") == "1")
+            p2p = os.environ.get("SHARD_P2P", "1") == "1"
+            if os.environ.get("SHARD_NCCL", "0") == "1":
+                coll.attach_nccl(lib, side.pf, peer_access=p2p)     # the library's own communicator
+            else:
+                coll.attach(lib, side.pf, peer_access=p2p)          # torch.distributed callbacks
         side.set_samples(cloud)            # replicated start on every rank
         log = []
         for step in range(3):
@@ -71,6 +85,10 @@ def main():
                 side.pf.contents.converged = 1
             side.update_sensor(scan, 30.0)
             neff = side.cur.n_effective
+            if recover:
+                side.pf.contents.w_slow = 1.0e-3      # w_diff = 0.4
+                side.pf.contents.w_fast = 0.6e-3
+                side.seed(1000 + step)                # the callback's libc stream; rank 0's poses are used
             side.resample()
             src = np.empty(n, np.int32)
             cnt = lib.amclb200_pf_resample_sources(side.pf, src.ctypes.data, n)
