@@ -194,7 +194,7 @@ float amclb200_inflate_last_ms(void);
 /* ---- several GPUs, one process each -------------------------------------------
  * Collectives are supplied by the host program (torch.distributed / NCCL in
  * bench.py).  Both act IN PLACE on DEVICE buffers and must be ordered with the
- * library's stream.  dtype: 0 = fp64, 1 = int32; op: 0 = sum, 1 = min, 2 = max.
+ * library's stream.  dtype: 0 = fp64, 1 = int32, 2 = int64; op: 0 = sum, 1 = min, 2 = max.
  * all-gather: rank r's block of bytes_per_rank bytes sits at offset
  * r * bytes_per_rank of d_buf on entry; all blocks are present on return. */
 typedef void (*amclb200_allreduce_fn)(void *d_buf, int count, int dtype, int op, void *user);

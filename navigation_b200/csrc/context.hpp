@@ -120,8 +120,12 @@ constexpr unsigned long long kEmptyKey = ~0ull;
 // device buffers and are stream-ordered with the library's stream.
 typedef void (*shard_allreduce_fn)(void *d_buf, int count, int dtype, int op, void *user);
 typedef void (*shard_allgather_fn)(void *d_buf, unsigned long long bytes_per_rank, void *user);
-enum { SHARD_F64 = 0, SHARD_I32 = 1 };
+enum { SHARD_F64 = 0, SHARD_I32 = 1, SHARD_I64 = 2 };
 enum { SHARD_SUM = 0, SHARD_MIN = 1, SHARD_MAX = 2 };
+
+constexpr int kShardTile = 1024;      // = the tile length of the exact cumulative table
+constexpr int kShardMaxAligned = 32;  // largest world with tile-aligned slices
+constexpr int kShardPad = kShardTile * (kShardMaxAligned + 1);   // extra records every particle array carries
 
 struct Shard
 {
@@ -135,8 +139,16 @@ struct Shard
   // shard_nccl.cu): collectives are enqueued on the library's stream straight
   // from C++, no host round trip through the caller.
   void *nccl_comm = nullptr;
+  // Slices are whole tiles of the cumulative table (cumsum_dev.cu), so that every
+  // rank can build its own part of the table; 1 when the world is too large for
+  // the padding the arrays carry (kShardPad).
+  int align = 1;
   bool on() const { return world > 1; }
-  int chunk(int n) const { return (n + world - 1) / world; }
+  int chunk(int n) const
+  {
+    const int per = (n + world - 1) / world;
+    return (per + align - 1) / align * align;
+  }
   int lo(int n) const { int v = rank * chunk(n); return v < n ? v : n; }
   int hi(int n) const { int v = (rank + 1) * chunk(n); return v < n ? v : n; }
   int count(int n) const { return hi(n) - lo(n); }
@@ -202,6 +214,9 @@ struct PfCtx
   unsigned long long *d_tile_fn = nullptr;  // 2 words per tile
   int *d_tile_class = nullptr;
   int tile_cap = 0;
+  double *d_dirty_w = nullptr;    // sharded table: weights of the tiles that need the element-wise walk
+  int *d_dirty_row = nullptr;     // tile -> row of d_dirty_w
+  int dirty_row_cap = 0;
 
   // laser staging: beam table, sized on demand; rank -> likelihood table, each
   // entry repeated lut_copies times, re-uploaded only when its version changes
@@ -293,6 +308,11 @@ inline Weights weights_of(const Particle *set)
   return w;
 }
 void exact_cumsum_w(PfCtx *c, Weights w, int n, double *d_cum);
+// Sharded form: every rank builds the table of its own (tile-aligned) slice from
+// the weights it owns, the ranks exchange only per-tile summaries, and the table
+// itself is all-gathered.  False: not applicable here (the caller uses the
+// replicated form); the result is the same table either way.
+bool exact_cumsum_sharded(PfCtx *c, const Particle *set, int n, double *d_cum);
 
 // exact sequential-order cumulative table (pf.c:399-402) of the weights of a set
 void exact_cumsum(PfCtx *c, const Particle *set, int n, double *d_cum);

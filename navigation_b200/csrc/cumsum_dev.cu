@@ -136,10 +136,11 @@ __device__ PairFn block_scan_fn(PairFn v, PairFn *total, PairFn *s_warp)
 // writes them out contiguously: the four later passes then read 8 B per weight
 // instead of dragging the whole record through the memory system each time.
 __global__ void cs_tile_sums(const Weights W, int n, double *__restrict__ tile_sum,
-                             double *__restrict__ tile_max, double *__restrict__ packed)
+                             double *__restrict__ tile_max, double *__restrict__ packed, int tile0)
 {
   __shared__ double s_red[32];
-  const int base = blockIdx.x * kTileLen;
+  const int tile = (int)blockIdx.x + tile0;
+  const int base = tile * kTileLen;
   double v = 0.0, mx = 0.0;
 #pragma unroll
   for (int k = 0; k < kPerThread; k++)
@@ -162,14 +163,17 @@ __global__ void cs_tile_sums(const Weights W, int n, double *__restrict__ tile_s
   if (threadIdx.x == 0)
   {
     for (int k = 1; k < (int)(blockDim.x >> 5); k++) mx = fmax(mx, s_red[k]);
-    tile_sum[blockIdx.x] = t;
-    tile_max[blockIdx.x] = mx;
+    tile_sum[tile] = t;
+    tile_max[tile] = mx;
   }
 }
 
 // ---- B: rough prefix of the tile sums and clean/dirty classification ---------
+// dirty_row (sharded table only): tile -> row of the buffer in which the owners of
+// the dirty tiles publish their weights; a count beyond max_rows raises *overflow.
 __global__ void cs_classify(const double *__restrict__ tile_sum, const double *__restrict__ tile_max,
-                            int tiles, int n, int *__restrict__ tile_class, int *dirty_count)
+                            int tiles, int n, int *__restrict__ tile_class, int *dirty_count,
+                            int *__restrict__ dirty_row, int max_rows, int *overflow)
 {
   __shared__ double s_part[1024];
   // pass 1: grand total (each thread a contiguous slab, then a serial combine)
@@ -217,19 +221,43 @@ __global__ void cs_classify(const double *__restrict__ tile_sum, const double *_
       if (e0 == e1 && e0 > -1020 && e0 < 1020) cls = e0;
     }
     tile_class[t] = cls;
-    if (cls == kDirty) atomicAdd(dirty_count, 1);
+    if (cls == kDirty)
+    {
+      const int row = atomicAdd(dirty_count, 1);
+      if (dirty_row)
+      {
+        dirty_row[t] = row < max_rows ? row : -1;
+        if (row >= max_rows) *overflow = 1;
+      }
+    }
+  }
+}
+
+// Sharded table: the owner of a dirty tile copies its weights into the tile's row.
+__global__ void cs_publish_dirty(const Weights W, int n, const int *__restrict__ tile_class,
+                                 const int *__restrict__ dirty_row, int tile0, double *__restrict__ rows)
+{
+  const int tile = (int)blockIdx.x + tile0;
+  if (tile_class[tile] != kDirty) return;
+  const int row = dirty_row[tile];
+  if (row < 0) return;
+  for (int k = threadIdx.x; k < kTileLen; k += blockDim.x)
+  {
+    const int i = tile * kTileLen + k;
+    rows[(size_t)row * kTileLen + k] = i < n ? W[i] : 0.0;
   }
 }
 
 // ---- C: composed function of every clean tile ----------------------------------
 __global__ void cs_tile_fns(const Weights W, int n, const int *__restrict__ tile_class,
-                            PairFn *__restrict__ tile_fn)
+                            PairFn *__restrict__ tile_fn, int tile0)
 {
   __shared__ PairFn s_warp[33];
-  const int cls = tile_class[blockIdx.x];
+  const int tile = (int)blockIdx.x + tile0;
+  const int cls = tile_class[tile];
   if (cls == kDirty || cls == kFlat) return;     // uniform across the block
   const int shift = 52 - cls;
-  const int first = blockIdx.x * kTileLen + threadIdx.x * kPerThread;
+  const int first = tile * kTileLen + threadIdx.x * kPerThread;
   PairFn f = fn_identity();
 #pragma unroll
   for (int k = 0; k < kPerThread; k++)
@@ -239,13 +267,16 @@ __global__ void cs_tile_fns(const Weights W, int n, const int *__restrict__ tile
   }
   PairFn total;
   block_scan_fn(f, &total, s_warp);
-  if (threadIdx.x == 0) tile_fn[blockIdx.x] = total;
+  if (threadIdx.x == 0) tile_fn[tile] = total;
 }
 
 // ---- D: exact carry into every tile; dirty tiles are walked here ---------------
+// dirty_rows / dirty_row: where the weights of the dirty tiles are read from in
+// the sharded table (this rank owns only some of them); null: from W itself.
 __global__ void cs_carries(const Weights W, int n, int tiles,
                            const int *__restrict__ tile_class, const PairFn *__restrict__ tile_fn,
-                           double *__restrict__ carry_in, double *__restrict__ cum)
+                           double *__restrict__ carry_in, double *__restrict__ cum,
+                           const double *__restrict__ dirty_rows, const int *__restrict__ dirty_row)
 {
   __shared__ PairFn s_warp[33];
   __shared__ double s_w[kTileLen];
@@ -330,10 +361,17 @@ __global__ void cs_carries(const Weights W, int n, int tiles,
       const int tt = base + d;
       const int a = tt * kTileLen;
       const int m = min(kTileLen, n - a);
-      for (int k = tid; k < m; k += blockDim.x) s_w[k] = W[a + k];
+      if (dirty_rows)
+      {
+        const int row = dirty_row[tt];
+        for (int k = tid; k < m; k += blockDim.x) s_w[k] = row >= 0 ? dirty_rows[(size_t)row * kTileLen + k] : 0.0;
+      }
+      else
+        for (int k = tid; k < m; k += blockDim.x) s_w[k] = W[a + k];
       __syncthreads();
       if (tid == 0)
       {
+        cum[a] = s_carry;      // (already there unless the tile opens a rank's slice)
         double run = s_carry;
         for (int k = 0; k < m; k++)
         {
@@ -353,23 +391,27 @@ __global__ void cs_carries(const Weights W, int n, int tiles,
 
 // ---- E: per-element table of the clean tiles ----------------------------------------
 __global__ void cs_apply(const Weights W, int n, const int *__restrict__ tile_class,
-                         const double *__restrict__ carry_in, double *__restrict__ cum)
+                         const double *__restrict__ carry_in, double *__restrict__ cum, int tile0)
 {
   __shared__ PairFn s_warp[33];
-  const int cls = tile_class[blockIdx.x];
+  const int tile = (int)blockIdx.x + tile0;
+  const int cls = tile_class[tile];
   if (cls == kDirty) return;
+  // the entry in front of the tile: written by the previous tile as well, except
+  // where that tile belongs to another rank
+  if (threadIdx.x == 0) cum[(size_t)tile * kTileLen] = carry_in[tile];
   if (cls == kFlat)
   {
-    const double v = carry_in[blockIdx.x];
+    const double v = carry_in[tile];
     for (int k = threadIdx.x; k < kTileLen; k += blockDim.x)
     {
-      const int i = blockIdx.x * kTileLen + k;
+      const int i = tile * kTileLen + k;
       if (i < n) cum[i + 1] = v;
     }
     return;
   }
   const int shift = 52 - cls;
-  const int first = blockIdx.x * kTileLen + threadIdx.x * kPerThread;
+  const int first = tile * kTileLen + threadIdx.x * kPerThread;
   double w[kPerThread];
   PairFn f = fn_identity();
 #pragma unroll
@@ -381,7 +423,7 @@ __global__ void cs_apply(const Weights W, int n, const int *__restrict__ tile_cl
   }
   PairFn total;
   const PairFn ex = block_scan_fn(f, &total, s_warp);
-  unsigned long long C = (unsigned long long)scalbn(carry_in[blockIdx.x], shift);
+  unsigned long long C = (unsigned long long)scalbn(carry_in[tile], shift);
   C = fn_apply(ex, C);
 #pragma unroll
   for (int k = 0; k < kPerThread; k++)
@@ -394,9 +436,11 @@ __global__ void cs_apply(const Weights W, int n, const int *__restrict__ tile_cl
 
 // ---- F: the defining recurrence, checked everywhere -------------------------------------
 __global__ void cs_verify(const Weights W, int n, const double *__restrict__ cum,
-                          int *bad)
+                          int *bad, int first, int count)
 {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= count) return;
+  const int i = first + t;
   if (i >= n) return;
   const double want = __dadd_rn(cum[i], W[i]);
   if (!(cum[i + 1] == want) || (i == 0 && cum[0] != 0.0)) *bad = 1;
@@ -410,19 +454,123 @@ int g_last_dirty = 0, g_last_tiles = 0;
 unsigned long long exact_cumsum_fallback_count() { return g_fallbacks; }
 void exact_cumsum_last_tiles(int out[2]) { out[0] = g_last_dirty; out[1] = g_last_tiles; }
 
+static void ensure_tile_scratch(PfCtx *c, int tiles)
+{
+  if (tiles <= c->tile_cap) return;
+  if (c->d_tile_sum) { cudaFree(c->d_tile_sum); cudaFree(c->d_tile_carry); cudaFree(c->d_tile_fn); cudaFree(c->d_tile_class); }
+  c->tile_cap = tiles + 64;
+  AMCL_CUDA(cudaMalloc(&c->d_tile_sum, sizeof(double) * (size_t)c->tile_cap));
+  AMCL_CUDA(cudaMalloc(&c->d_tile_carry, sizeof(double) * (size_t)c->tile_cap));
+  AMCL_CUDA(cudaMalloc(&c->d_tile_fn, sizeof(PairFn) * (size_t)c->tile_cap));
+  AMCL_CUDA(cudaMalloc(&c->d_tile_class, sizeof(int) * (size_t)c->tile_cap));
+}
+
+// ---- the table of a sharded filter ---------------------------------------------------
+//
+// Every rank owns a run of whole tiles (Shard::chunk is a multiple of the tile
+// length) and only its own weights.  The O(n) passes -- tile sums, tile
+// functions, the per-element table, the recurrence check -- run on the own tiles
+// only; what the ranks exchange is one record per TILE (sum + maximum for the
+// classification, the composed pair function of the clean tiles: 32 B per 1024
+// weights) and the weights of the few dirty tiles; the single-block pass that
+// turns those into the exact carry of every tile is repeated by everybody
+// (16 Ki tiles at 16 Mi particles).  The finished slices are then all-gathered:
+// 8 B per particle, like the weights before, but without the 7/8 of the table
+// work that every rank used to redo.  Same bits as the replicated form: it IS the
+// same algorithm, tile by tile.
+constexpr int kMaxDirtyRows = 96;
+
+bool exact_cumsum_sharded(PfCtx *c, const Particle *set, int n, double *d_cum)
+{
+  const Shard &sh = c->shard;
+  if (!sh.on() || sh.align != kTileLen || !globals().exact_cumsum_parallel || n < (1 << 16)) return false;
+  cudaStream_t st = globals().stream;
+  const int chunk = sh.chunk(n);                    // multiple of kTileLen
+  const int chunk_tiles = chunk / kTileLen;
+  const int tiles = (n + kTileLen - 1) / kTileLen;
+  const int tile0 = sh.rank * chunk_tiles;
+  int own = tiles - tile0;
+  if (own > chunk_tiles) own = chunk_tiles;
+  if (own < 0) own = 0;
+  ensure_tile_scratch(c, chunk_tiles * sh.world);
+  if (!c->d_dirty_w)
+    AMCL_CUDA(cudaMalloc(&c->d_dirty_w, sizeof(double) * (size_t)kMaxDirtyRows * kTileLen));
+  if (c->dirty_row_cap < c->tile_cap)
+  {
+    if (c->d_dirty_row) cudaFree(c->d_dirty_row);
+    c->dirty_row_cap = c->tile_cap;
+    AMCL_CUDA(cudaMalloc(&c->d_dirty_row, sizeof(int) * (size_t)c->dirty_row_cap));
+  }
+  PairFn *tile_fn = reinterpret_cast<PairFn *>(c->d_tile_fn);
+  if (!c->d_wpack) AMCL_CUDA(cudaMalloc(&c->d_wpack, sizeof(double) * (size_t)c->alloc_samples));
+  Weights W = weights_of(set);
+  // tiles beyond this rank's (and beyond the table's end) must not carry stale sums
+  AMCL_CUDA(cudaMemsetAsync(c->d_tile_sum + tile0, 0, sizeof(double) * (size_t)chunk_tiles, st));
+  AMCL_CUDA(cudaMemsetAsync(c->d_tile_carry + tile0, 0, sizeof(double) * (size_t)chunk_tiles, st));
+  if (own > 0)
+  {
+    cs_tile_sums<<<own, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_carry, c->d_wpack, tile0);
+    AMCL_LAUNCH_CHECK();
+  }
+  W.p = c->d_wpack;
+  W.stride = 1;
+  sh.allgather(c->d_tile_sum, (unsigned long long)chunk_tiles * sizeof(double));
+  sh.allgather(c->d_tile_carry, (unsigned long long)chunk_tiles * sizeof(double));   // the tile maxima
+  const int bad_slot = 8, dirty_slot = 9, overflow_slot = 10;
+  AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, 3 * sizeof(int), st));
+  cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, c->d_tile_carry, tiles, n, c->d_tile_class,
+                                 c->d_ints + dirty_slot, c->d_dirty_row, kMaxDirtyRows,
+                                 c->d_ints + overflow_slot);
+  AMCL_LAUNCH_CHECK();
+  AMCL_CUDA(cudaMemsetAsync(c->d_dirty_w, 0, sizeof(double) * (size_t)kMaxDirtyRows * kTileLen, st));
+  if (own > 0)
+  {
+    cs_tile_fns<<<own, kTileThreads, 0, st>>>(W, n, c->d_tile_class, tile_fn, tile0);
+    AMCL_LAUNCH_CHECK();
+    cs_publish_dirty<<<own, kTileThreads, 0, st>>>(W, n, c->d_tile_class, c->d_dirty_row, tile0, c->d_dirty_w);
+    AMCL_LAUNCH_CHECK();
+  }
+  sh.allgather(tile_fn, (unsigned long long)chunk_tiles * sizeof(PairFn));
+  // rows of tiles this rank does not own are zero here: the sum is a gather
+  sh.allreduce(c->d_dirty_w, kMaxDirtyRows * kTileLen, SHARD_F64, SHARD_SUM);
+  cs_carries<<<1, 1024, 0, st>>>(W, n, tiles, c->d_tile_class, tile_fn, c->d_tile_carry, d_cum,
+                                c->d_dirty_w, c->d_dirty_row);
+  AMCL_LAUNCH_CHECK();
+  if (own > 0)
+  {
+    cs_apply<<<own, kTileThreads, 0, st>>>(W, n, c->d_tile_class, c->d_tile_carry, d_cum, tile0);
+    AMCL_LAUNCH_CHECK();
+    const int first = tile0 * kTileLen;
+    const int count = (n - first < chunk ? n - first : chunk);
+    cs_verify<<<(count + 255) / 256, 256, 0, st>>>(W, n, d_cum, c->d_ints + bad_slot, first, count);
+    AMCL_LAUNCH_CHECK();
+  }
+  // entry i + 1 of the table belongs to the owner of weight i
+  sh.allgather(d_cum + 1, (unsigned long long)chunk * sizeof(double));
+  // one verdict for everybody: any rank's failed check, or too many dirty tiles
+  sh.allreduce(c->d_ints + bad_slot, 3, SHARD_I32, SHARD_MAX);
+  AMCL_CUDA(cudaMemcpyAsync(c->h_ints + bad_slot, c->d_ints + bad_slot, 3 * sizeof(int),
+                            cudaMemcpyDeviceToHost, st));
+  AMCL_CUDA(cudaStreamSynchronize(st));
+  g_last_dirty = c->h_ints[dirty_slot];
+  g_last_tiles = tiles;
+  if (c->h_ints[bad_slot] || c->h_ints[overflow_slot])
+  {
+    if (c->h_ints[bad_slot])
+    {
+      g_fallbacks++;
+      fprintf(stderr, "[amcl_b200] exact_cumsum (sharded): recurrence check failed; using the replicated table\n");
+    }
+    return false;
+  }
+  return true;
+}
+
 void exact_cumsum_parallel(PfCtx *c, Weights W, int n, double *d_cum)
 {
   cudaStream_t st = globals().stream;
   const int tiles = (n + kTileLen - 1) / kTileLen;
-  if (tiles > c->tile_cap)
-  {
-    if (c->d_tile_sum) { cudaFree(c->d_tile_sum); cudaFree(c->d_tile_carry); cudaFree(c->d_tile_fn); cudaFree(c->d_tile_class); }
-    c->tile_cap = tiles + 64;
-    AMCL_CUDA(cudaMalloc(&c->d_tile_sum, sizeof(double) * (size_t)c->tile_cap));
-    AMCL_CUDA(cudaMalloc(&c->d_tile_carry, sizeof(double) * (size_t)c->tile_cap));
-    AMCL_CUDA(cudaMalloc(&c->d_tile_fn, sizeof(PairFn) * (size_t)c->tile_cap));
-    AMCL_CUDA(cudaMalloc(&c->d_tile_class, sizeof(int) * (size_t)c->tile_cap));
-  }
+  ensure_tile_scratch(c, tiles);
   PairFn *tile_fn = reinterpret_cast<PairFn *>(c->d_tile_fn);
   double *packed = nullptr;
   if (W.stride != 1)
@@ -430,7 +578,7 @@ void exact_cumsum_parallel(PfCtx *c, Weights W, int n, double *d_cum)
     if (!c->d_wpack) AMCL_CUDA(cudaMalloc(&c->d_wpack, sizeof(double) * (size_t)c->alloc_samples));
     packed = c->d_wpack;
   }
-  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_carry, packed);
+  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_carry, packed, 0);
   AMCL_LAUNCH_CHECK();
   if (packed)
   {
@@ -440,15 +588,16 @@ void exact_cumsum_parallel(PfCtx *c, Weights W, int n, double *d_cum)
   const int bad_slot = 8, dirty_slot = 9;
   AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, 2 * sizeof(int), st));
   cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, c->d_tile_carry, tiles, n, c->d_tile_class,
-                                 c->d_ints + dirty_slot);
+                                 c->d_ints + dirty_slot, nullptr, 0, nullptr);
   AMCL_LAUNCH_CHECK();
-  cs_tile_fns<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_class, tile_fn);
+  cs_tile_fns<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_class, tile_fn, 0);
   AMCL_LAUNCH_CHECK();
-  cs_carries<<<1, 1024, 0, st>>>(W, n, tiles, c->d_tile_class, tile_fn, c->d_tile_carry, d_cum);
+  cs_carries<<<1, 1024, 0, st>>>(W, n, tiles, c->d_tile_class, tile_fn, c->d_tile_carry, d_cum, nullptr,
+                                nullptr);
   AMCL_LAUNCH_CHECK();
-  cs_apply<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_class, c->d_tile_carry, d_cum);
+  cs_apply<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_class, c->d_tile_carry, d_cum, 0);
   AMCL_LAUNCH_CHECK();
-  cs_verify<<<(n + 255) / 256, 256, 0, st>>>(W, n, d_cum, c->d_ints + bad_slot);
+  cs_verify<<<(n + 255) / 256, 256, 0, st>>>(W, n, d_cum, c->d_ints + bad_slot, 0, n);
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaMemcpyAsync(c->h_ints + bad_slot, c->d_ints + bad_slot, 2 * sizeof(int),
                             cudaMemcpyDeviceToHost, st));

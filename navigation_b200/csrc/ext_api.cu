@@ -197,6 +197,7 @@ void amclb200_pf_set_shard(pf_t *pf, int rank, int world, shard_allreduce_fn all
     AMCL_FATAL("amclb200_pf_set_shard: collectives are required when world > 1");
   c->shard.rank = rank;
   c->shard.world = world;
+  c->shard.align = world > 1 && world <= kShardMaxAligned ? kShardTile : 1;
   c->shard.cb_allreduce = allreduce;
   c->shard.cb_allgather = allgather;
   c->shard.user = user;

@@ -68,8 +68,8 @@ PfCtx *pf_ctx_create(pf_t *pf)
   ensure_device();
   PfCtx *c = new PfCtx();
   c->host = pf;
-  // arrays are padded so that world * ceil(n / world) slices always fit
-  const size_t maxs = (size_t)pf->max_samples + 1024;
+  // arrays are padded so that world * chunk(n) slices always fit (Shard::chunk)
+  const size_t maxs = (size_t)pf->max_samples + kShardPad;
   c->max_samples = pf->max_samples;
   c->alloc_samples = (int)maxs;
   c->hash_cap = next_pow2((unsigned int)(2 * maxs + 2));
@@ -123,6 +123,8 @@ void pf_ctx_release(pf_t *pf)
   if (c->d_tile_carry) cudaFree(c->d_tile_carry);
   if (c->d_tile_fn) cudaFree(c->d_tile_fn);
   if (c->d_tile_class) cudaFree(c->d_tile_class);
+  if (c->d_dirty_w) cudaFree(c->d_dirty_w);
+  if (c->d_dirty_row) cudaFree(c->d_dirty_row);
   cudaFreeHost(c->h_scalars);
   cudaFreeHost(c->h_ints);
   delete c;

@@ -568,22 +568,33 @@ __device__ __forceinline__ int resample_limit(int k, int min_samples, int max_sa
   return n;
 }
 
-// n = min over m of (m+1) with (m+1) > limit(k_m)   (pf.c:483)
-// Samples [base, base + count); k_m = k_offset + k_inclusive[m] (the offset is the
-// number of distinct bins first seen on lower ranks in a sharded run).
+// n = min over m of (m+1) with (m+1) > limit(k_m)   (pf.c:483), and with it
+// leaf_count = k_{n-1}: one 64-bit minimum over (m + 1) << 32 | k_m.  The last
+// candidate always offers (max_samples, k_last), the answer when nothing cuts.
+// Samples [base, base + count); k_m = k_offset + k_inclusive[m], the offset being
+// the number of distinct bins first seen on lower ranks of a sharded run (summed
+// here from the all-reduced per-rank counts: no trip to the host).
 __global__ void find_kld_cut(const unsigned int *__restrict__ k_inclusive, int base, int count,
-                             int k_offset, int min_samples, int max_samples, double pop_err,
-                             double pop_z, int *cut)
+                             const int *__restrict__ rank_counts, int rank, int min_samples,
+                             int max_samples, double pop_err, double pop_z, unsigned long long *cutk)
 {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= count) return;
+  int k_offset = 0;
+  for (int r = 0; r < rank; r++) k_offset += rank_counts[r];
   const int m = base + t;
   const int k = k_offset + (int)k_inclusive[m];
+  const unsigned long long mine = ((unsigned long long)(unsigned int)(m + 1) << 32) | (unsigned int)k;
+  if (m + 1 == max_samples)
+  {
+    atomicMin(cutk, mine);
+    return;
+  }
   // limit() only changes where k changes, but evaluating it everywhere keeps
   // the kernel branch-free; min_samples gives a cheap early reject.
   if (m + 1 <= min_samples) return;
-  if (m + 1 >= __ldcg(cut)) return;   // cannot lower the cut: skip the formula and the atomic
-  if (m + 1 > resample_limit(k, min_samples, max_samples, pop_err, pop_z)) atomicMin(cut, m + 1);
+  if (mine >= __ldcg(cutk)) return;   // cannot lower the cut: skip the formula and the atomic
+  if (m + 1 > resample_limit(k, min_samples, max_samples, pop_err, pop_z)) atomicMin(cutk, mine);
 }
 
 __global__ void set_uniform_weight(Particle *set, int n, double w)
@@ -1181,7 +1192,8 @@ static void sync_scalars(PfCtx *c, int first, int count)
 }
 
 // d_ints slots
-enum { I_DISTINCT = 0, I_CUT = 1, I_CLUSTERS = 2, I_OUTSIDE = 3, I_MOVED = 4, I_KCUT = 5, I_RANKCNT = 24 };
+enum { I_DISTINCT = 0, I_CUT = 1, I_CLUSTERS = 2, I_OUTSIDE = 3, I_MOVED = 4, I_KCUT = 5,
+       I_CUTK = 6 /* and 7: one 64-bit word */, I_RANKCNT = 24 };
 
 static void bin_sizes(const pf_sample_set_t *set, double *bx, double *by, double *bt)
 {
@@ -1544,7 +1556,12 @@ void run_resample(PfCtx *c)
     return;
   }
 
-  if (p2p)
+  if (p2p && exact_cumsum_sharded(c, c->d_set[ia], n_a, c->d_cum))
+  {
+    // every rank built its slice of the table from its own weights; the all-gather
+    // of the slices is also the rendezvous that makes the source set final
+  }
+  else if (p2p)
   {
     const int lo = sh.lo(n_a), cnt = sh.count(n_a);
     if (cnt > 0)
@@ -1794,37 +1811,21 @@ void run_resample(PfCtx *c)
         scan_u32(c, c->d_flag + lo_c, c->d_scan + lo_c, cnt_c, I_RANKCNT + sh.rank);
       }
       sh.allreduce(c->d_ints + I_RANKCNT, sh.world, SHARD_I32, SHARD_SUM, sh.user);
-      sync_ints(c, I_RANKCNT, sh.world);
-      int k_offset = 0;
-      for (int r = 0; r < sh.rank; r++) k_offset += h_cnt[r];
-      c->h_ints[I_CUT] = maxs;
-      AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_CUT, c->h_ints + I_CUT, sizeof(int),
-                                cudaMemcpyHostToDevice, st));
+      // (n, leaf_count) in one 64-bit minimum over all ranks, one trip to the host
+      unsigned long long *d_cutk = reinterpret_cast<unsigned long long *>(c->d_ints + I_CUTK);
+      AMCL_CUDA(cudaMemsetAsync(d_cutk, 0x7F, sizeof(unsigned long long), st));   // positive as an int64
       if (cnt_c > 0)
       {
-        find_kld_cut<<<blocks_for(cnt_c, 256), 256, 0, st>>>(c->d_scan, lo_c, cnt_c, k_offset,
-                                                             pf->min_samples, maxs, pf->pop_err,
-                                                             pf->pop_z, c->d_ints + I_CUT);
+        find_kld_cut<<<blocks_for(cnt_c, 256), 256, 0, st>>>(c->d_scan, lo_c, cnt_c, c->d_ints + I_RANKCNT,
+                                                             sh.rank, pf->min_samples, maxs, pf->pop_err,
+                                                             pf->pop_z, d_cutk);
         AMCL_LAUNCH_CHECK();
       }
-      sh.allreduce(c->d_ints + I_CUT, 1, SHARD_I32, SHARD_MIN, sh.user);
-      sync_ints(c, I_CUT, 1);
-      n = c->h_ints[I_CUT];
-      // leaf_count = k_{n-1}, known to the rank whose slice holds sample n-1
-      c->h_ints[I_KCUT] = 0;
-      if (n - 1 >= lo_c && n - 1 < lo_c + cnt_c)
-      {
-        unsigned int local_k = 0;
-        AMCL_CUDA(cudaMemcpyAsync(&local_k, c->d_scan + (n - 1), sizeof(unsigned int),
-                                  cudaMemcpyDeviceToHost, st));
-        AMCL_CUDA(cudaStreamSynchronize(st));
-        c->h_ints[I_KCUT] = k_offset + (int)local_k;
-      }
-      AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_KCUT, c->h_ints + I_KCUT, sizeof(int),
-                                cudaMemcpyHostToDevice, st));
-      sh.allreduce(c->d_ints + I_KCUT, 1, SHARD_I32, SHARD_MAX, sh.user);
-      sync_ints(c, I_KCUT, 1);
-      k_at_cut = (unsigned int)c->h_ints[I_KCUT];
+      sh.allreduce(d_cutk, 1, SHARD_I64, SHARD_MIN, sh.user);
+      sync_ints(c, I_CUTK, 2);
+      const unsigned long long cutk = *reinterpret_cast<unsigned long long *>(c->h_ints + I_CUTK);
+      n = (int)(cutk >> 32);
+      k_at_cut = (unsigned int)(cutk & 0xFFFFFFFFull);
     }
   }
   if (!shared_grid)
@@ -1836,18 +1837,15 @@ void run_resample(PfCtx *c)
     build_histogram(c, maxs);
     tr.mark("histogram");
     scan_u32(c, c->d_flag, c->d_scan, maxs, I_DISTINCT);
-    c->h_ints[I_CUT] = maxs;
-    AMCL_CUDA(cudaMemcpyAsync(c->d_ints + I_CUT, c->h_ints + I_CUT, sizeof(int),
-                              cudaMemcpyHostToDevice, st));
-    find_kld_cut<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_scan, 0, maxs, 0, pf->min_samples, maxs,
-                                                        pf->pop_err, pf->pop_z, c->d_ints + I_CUT);
+    unsigned long long *d_cutk = reinterpret_cast<unsigned long long *>(c->d_ints + I_CUTK);
+    AMCL_CUDA(cudaMemsetAsync(d_cutk, 0x7F, sizeof(unsigned long long), st));
+    find_kld_cut<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_scan, 0, maxs, nullptr, 0, pf->min_samples, maxs,
+                                                        pf->pop_err, pf->pop_z, d_cutk);
     AMCL_LAUNCH_CHECK();
-    sync_ints(c, I_CUT, 1);
-    n = c->h_ints[I_CUT];
-    // leaf_count = k_{n-1}
-    AMCL_CUDA(cudaMemcpyAsync(&k_at_cut, c->d_scan + (n - 1), sizeof(unsigned int),
-                              cudaMemcpyDeviceToHost, st));
-    AMCL_CUDA(cudaStreamSynchronize(st));
+    sync_ints(c, I_CUTK, 2);
+    const unsigned long long cutk = *reinterpret_cast<unsigned long long *>(c->h_ints + I_CUTK);
+    n = (int)(cutk >> 32);                               // pf.c:483
+    k_at_cut = (unsigned int)(cutk & 0xFFFFFFFFull);     // leaf_count = k_{n-1}
   }
   set_b->sample_count = n;
   set_b->kdtree->leaf_count = (int)k_at_cut;

@@ -28,7 +28,7 @@ namespace
 typedef struct ncclComm *ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 enum { ncclSuccess = 0 };
-enum { ncclInt8 = 0, ncclInt32 = 2, ncclFloat64 = 8 };
+enum { ncclInt8 = 0, ncclInt32 = 2, ncclInt64 = 4, ncclFloat64 = 8 };
 enum { ncclSum = 0, ncclProd = 1, ncclMax = 2, ncclMin = 3 };
 
 struct Api
@@ -79,7 +79,7 @@ Api &api()
 void nccl_allreduce(void *comm, void *d_buf, int count, int dtype, int op)
 {
   if (count <= 0) return;
-  const int dt = dtype == SHARD_F64 ? ncclFloat64 : ncclInt32;
+  const int dt = dtype == SHARD_F64 ? ncclFloat64 : (dtype == SHARD_I64 ? ncclInt64 : ncclInt32);
   const int o = op == SHARD_SUM ? ncclSum : (op == SHARD_MIN ? ncclMin : ncclMax);
   AMCL_NCCL(api().AllReduce(d_buf, d_buf, (size_t)count, dt, o, (ncclComm_t)comm, globals().stream));
 }
@@ -138,6 +138,7 @@ void amclb200_pf_set_shard_nccl(pf_t *pf, int rank, int world, const unsigned ch
   ensure_device();
   c->shard.rank = rank;
   c->shard.world = world;
+  c->shard.align = world > 1 && world <= kShardMaxAligned ? kShardTile : 1;
   c->shard.cb_allreduce = nullptr;
   c->shard.cb_allgather = nullptr;
   c->shard.user = nullptr;

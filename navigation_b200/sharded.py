@@ -6,7 +6,7 @@ only the rank's contiguous particle slice current and asks the host program for
 two in-place collectives on raw buffers (include/amcl_b200.h,
 amclb200_pf_set_shard):
 
-    allreduce(buf, count, dtype, op)      dtype 0 = fp64, 1 = int32; op sum/min/max
+    allreduce(buf, count, dtype, op)      dtype 0 = fp64, 1 = int32, 2 = int64; op sum/min/max
     allgather(buf, bytes_per_rank)        rank r's block already sits at r*bytes_per_rank
 
 `Collectives` implements both on torch.distributed.  On a GPU the buffers are
@@ -23,16 +23,29 @@ import torch.distributed as dist
 ALLREDUCE_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p)
 ALLGATHER_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64, C.c_void_p)
 
-F64, I32 = 0, 1
+F64, I32, I64 = 0, 1, 2
 SUM, MIN, MAX = 0, 1, 2
 
-_NP = {F64: (np.float64, "<f8", torch.float64, 8), I32: (np.int32, "<i4", torch.int32, 4)}
+_NP = {F64: (np.float64, "<f8", torch.float64, 8), I32: (np.int32, "<i4", torch.int32, 4),
+       I64: (np.int64, "<i8", torch.int64, 8)}
 _OPS = {SUM: dist.ReduceOp.SUM, MIN: dist.ReduceOp.MIN, MAX: dist.ReduceOp.MAX}
 
 
+SHARD_TILE, SHARD_MAX_ALIGNED = 1024, 32
+SHARD_PAD = SHARD_TILE * (SHARD_MAX_ALIGNED + 1)      # extra records every particle array carries
+
+
+def shard_chunk(n, world):
+    per = (n + world - 1) // world
+    align = SHARD_TILE if 1 < world <= SHARD_MAX_ALIGNED else 1
+    return (per + align - 1) // align * align
+
+
 def shard_range(n, rank, world):
-    """[lo, hi) of rank's slice of n items: chunks of ceil(n/world) (mirrors Shard in context.hpp)."""
-    chunk = (n + world - 1) // world
+    """[lo, hi) of rank's slice of n items (mirrors Shard in context.hpp): chunks of
+    ceil(n/world), rounded up to whole 1024-weight tiles of the cumulative table
+    for 2..32 ranks."""
+    chunk = shard_chunk(n, world)
     lo = min(rank * chunk, n)
     hi = min((rank + 1) * chunk, n)
     return lo, hi

@@ -51,7 +51,7 @@ def _worker(rank, world, port, q):
         # --- in-place allgather of 32-byte particle records -------------------
         n = 11
         lo, hi = sharded.shard_range(n, rank, world)
-        chunk = (n + world - 1) // world
+        chunk = sharded.shard_chunk(n, world)
         full = np.full((world * chunk, 4), -1.0)
         truth = np.arange(world * chunk * 4, dtype=np.float64).reshape(-1, 4)
         full[lo:hi] = truth[lo:hi]
@@ -79,7 +79,7 @@ def _worker(rank, world, port, q):
         whole[:, 3] /= total
         # two ranks: weight the slice, all-reduce the total, normalise, all-gather
         lo, hi = sharded.shard_range(n, rank, world)
-        chunk = (n + world - 1) // world
+        chunk = sharded.shard_chunk(n, world)
         mine = np.zeros((world * chunk, 4))
         mine[:n] = cloud
         part = np.ascontiguousarray(mine[lo:hi])
@@ -112,8 +112,9 @@ def test_shard_range_covers_everything():
                 got.extend([lo, hi])
             assert got[0] == 0 and got[-1] == n
             assert all(got[2 * r + 1] == got[2 * r + 2] for r in range(world - 1))
-            chunk = (n + world - 1) // world
-            assert world * chunk <= n + 1024      # the padding pf_ctx_create reserves
+            chunk = sharded.shard_chunk(n, world)
+            assert world * chunk <= n + sharded.SHARD_PAD      # the padding pf_ctx_create reserves
+            assert world == 1 or chunk % sharded.SHARD_TILE == 0
 
 
 def test_collectives_and_plan_world_size_2():
