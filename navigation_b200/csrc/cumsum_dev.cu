@@ -270,6 +270,168 @@ __global__ void cs_tile_fns(const Weights W, int n, const int *__restrict__ tile
   if (threadIdx.x == 0) tile_fn[tile] = total;
 }
 
+// ---- the same algorithm inside ONE block, on weights held in shared memory ------------
+//
+// Used twice: for the dirty 1024-weight tiles of a large table (cs_carries), so
+// that only the 32-weight stretch around a binade crossing is walked element by
+// element instead of the whole tile, and for the whole table of a node-sized
+// filter (cs_small: amcl_node runs 500 .. 10 000 particles, amcl/cfg/AMCL.cfg,
+// where a single-thread walk is the longest kernel of the update).  Sub-tiles of
+// 32 weights: warp sums classify them, a warp scan of pair functions gives each
+// clean sub-tile its function, one thread chains the sub-tiles in integer
+// arithmetic (converting only where the binade changes) and walks the few dirty
+// ones, then the warps write the entries.
+constexpr int kSubTile = 32;
+
+struct SubScratch           // shared memory for up to MAXT sub-tiles
+{
+  double *tsum, *tmax, *cin;
+  unsigned long long *cin_int;
+  int *cls;
+  PairFn *fn;
+  double *carry;            // one double: carry out
+};
+
+__device__ __forceinline__ int exponent_of(double v)   // ilogb for normal, positive v
+{
+  return (int)((__double_as_longlong(v) >> 52) & 0x7ff) - 1023;
+}
+__device__ __forceinline__ double pow2(int e)          // 2^e, |e| < 1022
+{
+  return __longlong_as_double((long long)(1023 + e) << 52);
+}
+
+// s_w[0..m): the weights; carry0: the table entry in front of them; n_total: the
+// length of the whole table (error margin of the rough prefix); out[k + 1] receives
+// the entry behind weight k.  All threads of the block must call; the carry out is
+// returned to all of them.
+__device__ double block_exact_table(const double *s_w, int m, double carry0, int n_total,
+                                    double *__restrict__ out, const SubScratch S)
+{
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+  const int tiles = (m + kSubTile - 1) / kSubTile;
+  // A: sum and maximum of every sub-tile
+  for (int t = warp; t < tiles; t += nwarps)
+  {
+    const int i = t * kSubTile + lane;
+    const double w = i < m ? s_w[i] : 0.0;
+    double v = w, mx = w;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+      v += __shfl_xor_sync(kFullMask, v, o);
+      mx = fmax(mx, __shfl_xor_sync(kFullMask, mx, o));
+    }
+    if (lane == 0) { S.tsum[t] = v; S.tmax[t] = mx; }
+  }
+  __syncthreads();
+  // B: rough prefix and classification (the margins of cs_classify)
+  if (tid == 0)
+  {
+    const double eps = 4.0 * (double)n_total * 1.1102230246251565e-16;
+    double run = carry0;
+    for (int t = 0; t < tiles; t++)
+    {
+      const double start = run * (1.0 - eps);
+      run += S.tsum[t];
+      const double end = run * (1.0 + eps);
+      int cls = kDirty;
+      if (S.tsum[t] == 0.0 || (start > 0.0 && S.tmax[t] < start * 2.7755575615628914e-17))
+        cls = kFlat;
+      else if (start > 0.0 && end < 1.0e300)
+      {
+        const int e0 = exponent_of(start), e1 = exponent_of(end);
+        if (e0 == e1 && e0 > -1020 && e0 < 1020) cls = e0;
+      }
+      S.cls[t] = cls;
+    }
+  }
+  __syncthreads();
+  // C: composed function of every clean sub-tile
+  for (int t = warp; t < tiles; t += nwarps)
+  {
+    const int cls = S.cls[t];
+    if (cls == kDirty || cls == kFlat) continue;            // uniform across the warp
+    const int i = t * kSubTile + lane;
+    PairFn inc = i < m ? fn_of_weight(s_w[i], 52 - cls) : fn_identity();
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+      const PairFn up = fn_shfl_up(inc, o);
+      if (lane >= o) inc = fn_compose(up, inc);
+    }
+    if (lane == 31) S.fn[t] = inc;
+  }
+  __syncthreads();
+  // D: the exact carry into every sub-tile; dirty ones are walked here
+  if (tid == 0)
+  {
+    double carry = carry0;
+    unsigned long long C = 0ull;
+    int e = 0;
+    bool as_int = false;
+    for (int t = 0; t < tiles; t++)
+    {
+      const int cls = S.cls[t];
+      if (cls != kDirty && cls != kFlat)
+      {
+        if (!as_int || e != cls)
+        {
+          if (as_int) carry = (double)C * pow2(e - 52);
+          C = (unsigned long long)(carry * pow2(52 - cls));    // exact: carry is a multiple of 2^(cls-52)
+          e = cls;
+          as_int = true;
+        }
+        S.cin_int[t] = C;
+        C = fn_apply(S.fn[t], C);
+        continue;
+      }
+      if (as_int)
+      {
+        carry = (double)C * pow2(e - 52);
+        as_int = false;
+      }
+      S.cin[t] = carry;
+      if (cls == kDirty)
+      {
+        const int a = t * kSubTile, cnt = min(kSubTile, m - a);
+        for (int k = 0; k < cnt; k++)
+        {
+          carry = __dadd_rn(carry, s_w[a + k]);
+          out[a + k + 1] = carry;
+        }
+      }
+    }
+    if (as_int) carry = (double)C * pow2(e - 52);
+    S.carry[0] = carry;
+  }
+  __syncthreads();
+  // E: the entries of the clean and flat sub-tiles
+  for (int t = warp; t < tiles; t += nwarps)
+  {
+    const int cls = S.cls[t];
+    if (cls == kDirty) continue;
+    const int i = t * kSubTile + lane;
+    if (cls == kFlat)
+    {
+      if (i < m) out[i + 1] = S.cin[t];
+      continue;
+    }
+    const int shift = 52 - cls;
+    PairFn inc = i < m ? fn_of_weight(s_w[i], shift) : fn_identity();
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+      const PairFn up = fn_shfl_up(inc, o);
+      if (lane >= o) inc = fn_compose(up, inc);
+    }
+    if (i < m) out[i + 1] = (double)fn_apply(inc, S.cin_int[t]) * pow2(-shift);
+  }
+  const double result = S.carry[0];
+  __syncthreads();
+  return result;
+}
+
 // ---- D: exact carry into every tile; dirty tiles are walked here ---------------
 // dirty_rows / dirty_row: where the weights of the dirty tiles are read from in
 // the sharded table (this rank owns only some of them); null: from W itself.
@@ -283,6 +445,14 @@ __global__ void cs_carries(const Weights W, int n, int tiles,
   __shared__ double s_carry;
   __shared__ int s_min[32];
   __shared__ int s_first_dirty, s_run_class;
+  constexpr int kSub = kTileLen / kSubTile;
+  __shared__ double s_sub_d[3 * kSub + 1];
+  __shared__ unsigned long long s_sub_c[kSub];
+  __shared__ int s_sub_cls[kSub];
+  __shared__ PairFn s_sub_fn[kSub];
+  SubScratch sub;
+  sub.tsum = s_sub_d; sub.tmax = s_sub_d + kSub; sub.cin = s_sub_d + 2 * kSub; sub.carry = s_sub_d + 3 * kSub;
+  sub.cin_int = s_sub_c; sub.cls = s_sub_cls; sub.fn = s_sub_fn;
   const int tid = threadIdx.x;
   if (tid == 0)
   {
@@ -369,19 +539,12 @@ __global__ void cs_carries(const Weights W, int n, int tiles,
       else
         for (int k = tid; k < m; k += blockDim.x) s_w[k] = W[a + k];
       __syncthreads();
-      if (tid == 0)
       {
-        cum[a] = s_carry;      // (already there unless the tile opens a rank's slice)
-        double run = s_carry;
-        for (int k = 0; k < m; k++)
-        {
-          run = __dadd_rn(run, s_w[k]);
-          s_w[k] = run;
-        }
-        s_carry = run;
+        // only the 32-weight stretches that may hold a crossing are walked
+        if (tid == 0) cum[a] = s_carry;      // (already there unless the tile opens a rank's slice)
+        const double carry_out = block_exact_table(s_w, m, s_carry, n, cum + a, sub);
+        if (tid == 0) s_carry = carry_out;
       }
-      __syncthreads();
-      for (int k = tid; k < m; k += blockDim.x) cum[a + k + 1] = s_w[k];
       cursor = d + 1;
       __syncthreads();
     }
@@ -446,12 +609,74 @@ __global__ void cs_verify(const Weights W, int n, const double *__restrict__ cum
   if (!(cum[i + 1] == want) || (i == 0 && cum[0] != 0.0)) *bad = 1;
 }
 
+// ---- node-sized filters: the whole table in one launch, nothing returns to the host ---
+constexpr int kSmallMaxTiles = 512;                       // n <= 16384
+__device__ unsigned long long g_small_fallbacks_dev = 0;
+
+__global__ void __launch_bounds__(1024)
+cs_small(const Weights W, int n, double *__restrict__ cum)
+{
+  extern __shared__ double s_w[];                          // n weights
+  __shared__ double s_d[3 * kSmallMaxTiles + 1];
+  __shared__ unsigned long long s_c[kSmallMaxTiles];
+  __shared__ int s_cls[kSmallMaxTiles];
+  __shared__ PairFn s_fn[kSmallMaxTiles];
+  __shared__ int s_bad;
+  SubScratch sub;
+  sub.tsum = s_d; sub.tmax = s_d + kSmallMaxTiles; sub.cin = s_d + 2 * kSmallMaxTiles;
+  sub.carry = s_d + 3 * kSmallMaxTiles;
+  sub.cin_int = s_c; sub.cls = s_cls; sub.fn = s_fn;
+  const int tid = threadIdx.x;
+  if (tid == 0)
+  {
+    s_bad = 0;
+    cum[0] = 0.0;
+  }
+  for (int i = tid; i < n; i += blockDim.x) s_w[i] = W[i];
+  __syncthreads();
+  block_exact_table(s_w, n, 0.0, n, cum, sub);
+  // the defining recurrence, everywhere (this block's own global writes)
+  for (int i = tid; i < n; i += blockDim.x)
+    if (!(cum[i + 1] == __dadd_rn(cum[i], s_w[i]))) s_bad = 1;
+  __syncthreads();
+  if (s_bad && tid == 0)
+  {
+    atomicAdd(&g_small_fallbacks_dev, 1ull);
+    double run = 0.0;
+    for (int i = 0; i < n; i++)
+    {
+      run = __dadd_rn(run, s_w[i]);
+      cum[i + 1] = run;
+    }
+  }
+}
+
 unsigned long long g_fallbacks = 0;
 int g_last_dirty = 0, g_last_tiles = 0;
 
 }  // namespace
 
-unsigned long long exact_cumsum_fallback_count() { return g_fallbacks; }
+unsigned long long exact_cumsum_fallback_count()
+{
+  unsigned long long small = 0;
+  if (globals().device >= 0)
+    AMCL_CUDA(cudaMemcpyFromSymbol(&small, g_small_fallbacks_dev, sizeof(small)));   // waits for the device
+  return g_fallbacks + small;
+}
+
+// n <= 16384: one launch, no trip to the host.
+void exact_cumsum_small(Weights W, int n, double *d_cum)
+{
+  static bool attr_set = false;
+  if (!attr_set)
+  {
+    AMCL_CUDA(cudaFuncSetAttribute(cs_small, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(sizeof(double) * kSubTile * kSmallMaxTiles)));
+    attr_set = true;
+  }
+  cs_small<<<1, 1024, sizeof(double) * (size_t)(n > 0 ? n : 1), globals().stream>>>(W, n, d_cum);
+  AMCL_LAUNCH_CHECK();
+}
 void exact_cumsum_last_tiles(int out[2]) { out[0] = g_last_dirty; out[1] = g_last_tiles; }
 
 static void ensure_tile_scratch(PfCtx *c, int tiles)

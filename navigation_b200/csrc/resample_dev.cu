@@ -242,10 +242,14 @@ void launch_cumsum_sequential(Weights W, int n, double *d_cum)
   AMCL_LAUNCH_CHECK();
 }
 
+void exact_cumsum_small(Weights W, int n, double *d_cum);   // cumsum_dev.cu
+
 void exact_cumsum_w(PfCtx *c, Weights W, int n, double *d_cum)
 {
-  if (globals().exact_cumsum_parallel && n >= 16384)
+  if (globals().exact_cumsum_parallel && n > 16384)
     exact_cumsum_parallel(c, W, n, d_cum);
+  else if (globals().exact_cumsum_parallel && n >= 64)
+    exact_cumsum_small(W, n, d_cum);
   else
     launch_cumsum_sequential(W, n, d_cum);
 }
