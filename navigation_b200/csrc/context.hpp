@@ -241,7 +241,12 @@ struct PfCtx
 
   // last-call timings (ms, CUDA events), for bench/diagnostics
   float ms_action = 0, ms_sensor = 0, ms_resample = 0;
+  cudaEvent_t ev_stage[3][2] = {{nullptr, nullptr}, {nullptr, nullptr}, {nullptr, nullptr}};
+  bool stage_pending[3] = {false, false, false};
   float ms_sensor_kernel = 0;     // the laser-model kernel alone
+  bool sensor_kernel_pending = false;  // ev_a / ev_b recorded, not read yet
+  bool defer_total = false;       // pf_update_sensor is calling one of the library's own models: the
+                                  // total weight stays on the device until the normalisation reads it
   long long sensor_evals = 0;     // particle-beam evaluations of that launch
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;
 };
@@ -338,12 +343,16 @@ struct ApiRange
   ~ApiRange();
 };
 
+// Device time of one API call (action / sensor / resample): two events on the
+// library's stream, kept in the filter's context.  Nothing waits for them here;
+// amclb200_pf_last_timings() resolves them when somebody asks.
 struct StageTimer
 {
-  cudaEvent_t a, b;
-  float *out;
-  explicit StageTimer(float *dst);
+  PfCtx *c;
+  int stage;   // 0 action, 1 sensor, 2 resample
+  StageTimer(PfCtx *ctx, int which_stage);
   ~StageTimer();
 };
+void stage_times_resolve(PfCtx *c);   // fills ms_action / ms_sensor / ms_resample
 
 }  // namespace amclb200

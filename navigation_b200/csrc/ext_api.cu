@@ -90,6 +90,7 @@ int amclb200_pf_cumulative_table(pf_t *pf, double *out, int capacity)
 void amclb200_pf_last_timings(pf_t *pf, float out_ms[3])
 {
   PfCtx *c = pf_ctx(pf);
+  stage_times_resolve(c);
   out_ms[0] = c->ms_action;
   out_ms[1] = c->ms_sensor;
   out_ms[2] = c->ms_resample;
@@ -249,6 +250,12 @@ void amclb200_set_parallel_cumsum(int on) { globals().exact_cumsum_parallel = on
 void amclb200_pf_sensor_kernel_stats(pf_t *pf, double out[2])
 {
   PfCtx *c = pf_ctx(pf);
+  if (c->sensor_kernel_pending && c->ev_b)
+  {
+    AMCL_CUDA(cudaEventSynchronize(c->ev_b));
+    AMCL_CUDA(cudaEventElapsedTime(&c->ms_sensor_kernel, c->ev_a, c->ev_b));
+    c->sensor_kernel_pending = false;
+  }
   out[0] = (double)c->ms_sensor_kernel;
   out[1] = (double)c->sensor_evals;
 }

@@ -90,20 +90,32 @@ void Trace::report(const char *what)
 ApiRange::ApiRange(const char *name) { nvtxRangePushA(name); }
 ApiRange::~ApiRange() { nvtxRangePop(); }
 
-StageTimer::StageTimer(float *dst) : out(dst)
+StageTimer::StageTimer(PfCtx *ctx, int which_stage) : c(ctx), stage(which_stage)
 {
-  AMCL_CUDA(cudaEventCreate(&a));
-  AMCL_CUDA(cudaEventCreate(&b));
-  AMCL_CUDA(cudaEventRecord(a, globals().stream));
+  if (!c->ev_stage[stage][0])
+  {
+    AMCL_CUDA(cudaEventCreate(&c->ev_stage[stage][0]));
+    AMCL_CUDA(cudaEventCreate(&c->ev_stage[stage][1]));
+  }
+  AMCL_CUDA(cudaEventRecord(c->ev_stage[stage][0], globals().stream));
 }
 
 StageTimer::~StageTimer()
 {
-  AMCL_CUDA(cudaEventRecord(b, globals().stream));
-  AMCL_CUDA(cudaEventSynchronize(b));
-  AMCL_CUDA(cudaEventElapsedTime(out, a, b));
-  cudaEventDestroy(a);
-  cudaEventDestroy(b);
+  AMCL_CUDA(cudaEventRecord(c->ev_stage[stage][1], globals().stream));
+  c->stage_pending[stage] = true;
+}
+
+void stage_times_resolve(PfCtx *c)
+{
+  float *dst[3] = {&c->ms_action, &c->ms_sensor, &c->ms_resample};
+  for (int k = 0; k < 3; k++)
+  {
+    if (!c->stage_pending[k]) continue;
+    AMCL_CUDA(cudaEventSynchronize(c->ev_stage[k][1]));
+    AMCL_CUDA(cudaEventElapsedTime(dst[k], c->ev_stage[k][0], c->ev_stage[k][1]));
+    c->stage_pending[k] = false;
+  }
 }
 
 // ----------------------------------------------------------------- registry --

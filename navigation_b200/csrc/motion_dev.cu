@@ -325,7 +325,7 @@ bool AMCLOdom::UpdateAction(pf_t *pf, AMCLSensorData *data)
   }
 
   ApiRange range("amcl_b200:AMCLOdom::UpdateAction");
-  StageTimer timer(&c->ms_action);
+  StageTimer timer(c, 0);
   const int n = pf->sets[which].sample_count;
   if (globals().rng == RNG_DRAND48)
   {

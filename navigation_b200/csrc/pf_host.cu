@@ -107,6 +107,9 @@ void pf_ctx_release(pf_t *pf)
   for (int j = 0; j < 2; j++) if (c->d_peer_tab[j]) cudaFree((void *)c->d_peer_tab[j]);
   if (c->d_wpack) cudaFree(c->d_wpack);
   if (c->shard.nccl_comm) nccl_release(c->shard.nccl_comm);
+  for (int k = 0; k < 3; k++)
+    for (int j = 0; j < 2; j++)
+      if (c->ev_stage[k][j]) cudaEventDestroy(c->ev_stage[k][j]);
   cudaFree(c->d_cum); cudaFree(c->d_draws); cudaFree(c->d_src); cudaFree(c->d_label);
   cudaFree(c->d_keys); cudaFree(c->d_slot); cudaFree(c->d_flag); cudaFree(c->d_scan);
   cudaFree(c->d_scan_tiles); cudaFree(c->d_tab_key); cudaFree(c->d_tab_first); cudaFree(c->d_tab_aux); cudaFree(c->d_scalars); cudaFree(c->d_ints);
@@ -379,10 +382,13 @@ void pf_update_sensor(pf_t *pf, pf_sensor_model_fn_t sensor_fn, void *sensor_dat
   PfCtx *c = pf_ctx(pf);
   const int which = pf->current_set;
   pf_sample_set_t *set = pf->sets + which;
-  StageTimer timer(&c->ms_sensor);
+  StageTimer timer(c, 1);
   double total;
   if (amcl::amclb200_is_device_laser_model(sensor_fn))
+  {
+    c->defer_total = true;                       // the total is fetched once, with n_effective
     total = (*sensor_fn)(sensor_data, set);      // device kernel, see sensor_dev.cu
+  }
   else
   {
     pf_pull(c, which);
@@ -390,6 +396,7 @@ void pf_update_sensor(pf_t *pf, pf_sensor_model_fn_t sensor_fn, void *sensor_dat
     pf_push(c, which);
   }
   run_sensor_normalise(c, which, total);
+  c->defer_total = false;
   pf_after_update(c, which);
 }
 
@@ -398,7 +405,7 @@ void pf_update_resample(pf_t *pf)
 {
   ApiRange range("amcl_b200:pf_update_resample");
   PfCtx *c = pf_ctx(pf);
-  StageTimer timer(&c->ms_resample);
+  StageTimer timer(c, 2);
   run_resample(c);
   pf_after_update(c, pf->current_set);
 }

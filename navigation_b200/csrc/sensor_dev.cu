@@ -597,10 +597,13 @@ __global__ void calc_ranges_kernel(const BeamArgs a, const double *__restrict__ 
 // ------------------------------------------------ normalisation (pf.c:282-316) --
 
 // total > 0: w /= total, accumulates sum w^2 per block.  total <= 0: w = 1/n.
+// total_dev: the total still sits on the device (the library's own laser models
+// leave it there, so that a sensor update costs one trip to the host, not two).
 __global__ void normalise_weights(Particle *set, int n, double total, double uniform,
-                                  double *block_sq)
+                                  double *block_sq, const double *total_dev)
 {
   __shared__ double s_red[32];
+  if (total_dev) total = *total_dev;
   double sq = 0.0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
   {
@@ -838,11 +841,11 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
     c->shard.allreduce(c->d_scalars, 1, SHARD_F64, SHARD_SUM, c->shard.user);
     c->replicated[which] = false;
   }
-  const double total = read_scalar(c, 0);  // also orders the staging vectors' lifetime
-  AMCL_CUDA(cudaEventElapsedTime(&c->ms_sensor_kernel, c->ev_a, c->ev_b));
   c->sensor_evals = (long long)n * nb;
   c->host_fresh[which] = false;
-  return total;
+  c->sensor_kernel_pending = true;         // ev_a / ev_b are read when somebody asks for the time
+  if (c->defer_total) return 0.0;          // pf_update_sensor picks the total up together with n_effective
+  return read_scalar(c, 0);
 }
 
 double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3],
@@ -910,9 +913,9 @@ double run_beam_model(PfCtx *c, int which, MapCtx *m, const double laser_pose[3]
     c->shard.allreduce(c->d_scalars, 1, SHARD_F64, SHARD_SUM, c->shard.user);
     c->replicated[which] = false;
   }
-  const double total = read_scalar(c, 0);
   c->host_fresh[which] = false;
-  return total;
+  if (c->defer_total) return 0.0;
+  return read_scalar(c, 0);
 }
 
 void run_sensor_normalise(PfCtx *c, int which, double total)
@@ -929,15 +932,33 @@ void run_sensor_normalise(PfCtx *c, int which, double total)
   int need_blocks = (cnt + 255) / 256;
   if (grid > need_blocks) grid = need_blocks > 0 ? need_blocks : 1;
   ensure_partials(c, grid);
-  normalise_weights<<<grid, 256, 0, st>>>(c->d_set[which] + lo, cnt, total, 1.0 / n, c->d_partials);
+  const bool deferred = c->defer_total;
+  normalise_weights<<<grid, 256, 0, st>>>(c->d_set[which] + lo, cnt, total, 1.0 / n, c->d_partials,
+                                          deferred ? c->d_scalars : nullptr);
   AMCL_LAUNCH_CHECK();
   double neff = 0.0;
-  if (total > 0.0)
+  if (deferred)
   {
+    // total (slot 0, left there by the laser model) and the sum of squares (slot 1)
+    // come back together: the one trip to the host of this update
     finish_partials<<<1, 256, 0, st>>>(c->d_partials, grid, c->d_scalars, 1);
     AMCL_LAUNCH_CHECK();
     if (slice) c->shard.allreduce(c->d_scalars + 1, 1, SHARD_F64, SHARD_SUM, c->shard.user);
-    neff = read_scalar(c, 1);
+    AMCL_CUDA(cudaMemcpyAsync(c->h_scalars, c->d_scalars, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    AMCL_CUDA(cudaStreamSynchronize(st));
+    total = c->h_scalars[0];
+  }
+  if (total > 0.0)
+  {
+    if (deferred)
+      neff = c->h_scalars[1];
+    else
+    {
+      finish_partials<<<1, 256, 0, st>>>(c->d_partials, grid, c->d_scalars, 1);
+      AMCL_LAUNCH_CHECK();
+      if (slice) c->shard.allreduce(c->d_scalars + 1, 1, SHARD_F64, SHARD_SUM, c->shard.user);
+      neff = read_scalar(c, 1);
+    }
     // pf.c:293-302.  w_avg accumulates the very numbers the model summed into
     // `total`, in the same order, so it equals total / n.
     double w_avg = total / n;
