@@ -441,7 +441,16 @@ struct BinTable
   int dense;
   int x0, y0, t0;            // dense: smallest key per axis
   int ex, ey, et;            // dense: extent per axis
+  // Number of samples the table is valid for when the host does not know it yet
+  // (the single-trip path of small filters): high word of the (n, k) pair
+  // find_kld_cut left on the device.  Null: the kernels' n_valid argument counts.
+  const unsigned long long *n_dev;
 };
+
+__device__ __forceinline__ unsigned int table_valid(const BinTable &T, int n_valid)
+{
+  return T.n_dev ? (unsigned int)(__ldg(T.n_dev) >> 32) : (unsigned int)n_valid;
+}
 
 __host__ __device__ inline void unpack_key(unsigned long long k, int *kx, int *ky, int *kt)
 {
@@ -647,7 +656,7 @@ __device__ __forceinline__ void uf_union(unsigned int *aux, unsigned int a, unsi
 __global__ void cc_init(const BinTable T, unsigned int nslots, int n_valid, unsigned int *cmin)
 {
   const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (s >= nslots || T.first[s] >= table_valid(T, n_valid)) return;
   T.aux[s] = s;
   cmin[s] = 0xFFFFFFFFu;
 }
@@ -658,7 +667,7 @@ __global__ void cc_init(const BinTable T, unsigned int nslots, int n_valid, unsi
 __global__ void cc_link(const BinTable T, unsigned int nslots, int n_valid)
 {
   const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (s >= nslots || T.first[s] >= table_valid(T, n_valid)) return;
   if (T.dense)
   {
     const int ix = (int)(s % (unsigned)T.ex);
@@ -672,7 +681,7 @@ __global__ void cc_link(const BinTable T, unsigned int nslots, int n_valid)
           (unsigned)nt >= (unsigned)T.et)
         continue;
       const unsigned int nb = (unsigned int)((nt * T.ey + ny) * T.ex + nx);
-      if (T.first[nb] < (unsigned int)n_valid) uf_union(T.aux, s, nb);
+      if (T.first[nb] < table_valid(T, n_valid)) uf_union(T.aux, s, nb);
     }
     return;
   }
@@ -688,7 +697,7 @@ __global__ void cc_link(const BinTable T, unsigned int nslots, int n_valid)
       if (kk == kEmptyKey) break;
       if (kk == nk)
       {
-        if (T.first[h] < (unsigned int)n_valid) uf_union(T.aux, s, h);
+        if (T.first[h] < table_valid(T, n_valid)) uf_union(T.aux, s, h);
         break;
       }
       h = (h + 1) & T.mask;
@@ -746,7 +755,7 @@ cc_brick_local(const BinTable T, int bricks_x, int bricks_y, int n_valid, unsign
   const int ix = bx * kBrickX + lx, iy = by * kBrickY + ly, it = bt * kBrickT + lt;
   const bool inside = ix < T.ex && iy < T.ey && it < T.et;
   const unsigned int s = inside ? (unsigned int)((it * T.ey + iy) * T.ex + ix) : 0u;
-  const bool occ = inside && T.first[s] < (unsigned int)n_valid;
+  const bool occ = inside && T.first[s] < table_valid(T, n_valid);
   s_lab[threadIdx.x] = threadIdx.x;
   s_occ[threadIdx.x] = occ ? 1 : 0;
   __syncthreads();
@@ -810,7 +819,7 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int 
   // forward neighbours with dx or dy = -1 leave the brick) have work to do
   if (lx != 0 && lx != kBrickX - 1 && ly != 0 && ly != kBrickY - 1 && lt != kBrickT - 1) return;
   const unsigned int s = (unsigned int)((it * T.ey + iy) * T.ex + ix);
-  if (T.first[s] >= (unsigned int)n_valid) return;
+  if (T.first[s] >= table_valid(T, n_valid)) return;
   for (int q = 14; q < 27; q++)
   {
     const int dt = q / 9 - 1, dy = (q % 9) / 3 - 1, dx = (q % 9) % 3 - 1;
@@ -828,14 +837,14 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int 
       if (same_owner != (phase == 1)) continue;
     }
     const unsigned int nb = (unsigned int)((nt * T.ey + ny) * T.ex + nx);
-    if (T.first[nb] >= (unsigned int)n_valid) continue;
+    if (T.first[nb] >= table_valid(T, n_valid)) continue;
     // same pruning as in cc_brick_local, now with any cell of the grid in between
     bool implied = false;
     if ((dx != 0) + (dy != 0) + (dt != 0) >= 2)
     {
-      if (dx != 0 && T.first[(nt * T.ey + ny) * T.ex + ix] < (unsigned int)n_valid) implied = true;
-      if (!implied && dy != 0 && T.first[(nt * T.ey + iy) * T.ex + nx] < (unsigned int)n_valid) implied = true;
-      if (!implied && dt != 0 && T.first[(it * T.ey + ny) * T.ex + nx] < (unsigned int)n_valid) implied = true;
+      if (dx != 0 && T.first[(nt * T.ey + ny) * T.ex + ix] < table_valid(T, n_valid)) implied = true;
+      if (!implied && dy != 0 && T.first[(nt * T.ey + iy) * T.ex + nx] < table_valid(T, n_valid)) implied = true;
+      if (!implied && dt != 0 && T.first[(it * T.ey + ny) * T.ex + nx] < table_valid(T, n_valid)) implied = true;
     }
     if (!implied) uf_union(T.aux, s, nb);
   }
@@ -847,7 +856,7 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int 
 __global__ void cc_flatten(const BinTable T, unsigned int nslots, int n_valid)
 {
   const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (s >= nslots || T.first[s] >= table_valid(T, n_valid)) return;
   unsigned int p = __ldcg(&T.aux[s]);
   for (;;)
   {
@@ -868,7 +877,7 @@ __global__ void cc_collect_roots(const BinTable T, unsigned int nslots, int n_va
                                  unsigned int *keys, int *count)
 {
   const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (s >= nslots || T.first[s] >= table_valid(T, n_valid)) return;
   if (T.aux[s] != s) return;
   const int k = atomicAdd(count, 1);
   if (k < kRootListCap)
@@ -880,9 +889,10 @@ __global__ void cc_collect_roots(const BinTable T, unsigned int nslots, int n_va
 
 // id of a root = number of roots whose earliest sample comes before its own
 __global__ void cc_rank_roots(const unsigned int *__restrict__ list, const unsigned int *__restrict__ keys,
-                              int count, unsigned int *cmin_to_id)
+                              int count, unsigned int *cmin_to_id, const int *count_dev = nullptr)
 {
   __shared__ unsigned int s_keys[256];
+  if (count_dev) count = min(*count_dev, kRootListCap);
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned int mine = t < count ? keys[t] : 0u;
   unsigned int rank = 0;
@@ -904,7 +914,7 @@ __global__ void cc_component_min(const BinTable T, unsigned int nslots, int n_va
   const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= nslots) return;
   const unsigned int f = T.first[s];
-  if (f >= (unsigned int)n_valid) return;
+  if (f >= table_valid(T, n_valid)) return;
   // A giant component would otherwise serialise millions of atomics on one
   // address: lanes of a warp that share a root combine first, and the group's
   // leader looks before it competes.
@@ -927,7 +937,7 @@ __global__ void cc_flag_roots(const BinTable T, unsigned int nslots, int n_valid
                               const unsigned int *__restrict__ cmin, unsigned int *cflag)
 {
   const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (s >= nslots || T.first[s] >= table_valid(T, n_valid)) return;
   if (T.aux[s] == s) cflag[cmin[s]] = 1u;
 }
 
@@ -935,7 +945,7 @@ __global__ void cc_assign_ids(const BinTable T, unsigned int nslots, int n_valid
                               const unsigned int *__restrict__ cscan, unsigned int *cmin_to_id)
 {
   const unsigned int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= nslots || T.first[s] >= (unsigned int)n_valid) return;
+  if (s >= nslots || T.first[s] >= table_valid(T, n_valid)) return;
   if (T.aux[s] == s) cmin_to_id[s] = cscan[cmin_to_id[s]] - 1u;   // cmin[root] -> cluster id
 }
 
@@ -966,9 +976,11 @@ __global__ void cluster_accumulate(const Particle *__restrict__ set, int n,
                                    const unsigned int *__restrict__ root_of_slot,
                                    const unsigned int *__restrict__ slot_of,
                                    const unsigned int *__restrict__ cid_of_root, double *acc,
-                                   int *label_out, int first)
+                                   int *label_out, int first, const unsigned long long *n_dev = nullptr)
 {
-  // samples [first, first + n) of the set (a sharded rank sums its own slice)
+  // samples [first, first + n) of the set (a sharded rank sums its own slice);
+  // n_dev: the count is the high word of the (n, k) pair still on the device
+  if (n_dev) n = (int)(__ldg(n_dev) >> 32);
   set += first;
   slot_of += first;
   if (label_out) label_out += first;
@@ -1162,6 +1174,55 @@ __global__ void copy_scaled(const Particle *__restrict__ src, Particle *dst, int
   store_particle(dst + i, s);
 }
 
+// ---- single-trip path of small filters: kernels that take n from the device ----------
+
+// pf.c:493-498 for a set whose size the host has not seen yet
+__global__ void set_uniform_weight_dev(Particle *set, int max_n, const unsigned long long *cutk)
+{
+  const int n = (int)(__ldg(cutk) >> 32);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && i < max_n) set[i].w = 1.0 / (double)n;
+}
+
+// pf_update_converged (pf.c:220-251) in one block: mean x / y in a fixed order,
+// then "is any sample farther than the threshold from it".  out[0] = 1 if so.
+__global__ void __launch_bounds__(1024)
+converged_small(const Particle *__restrict__ set, const unsigned long long *cutk, double thr, int *out)
+{
+  __shared__ double s_red[32];
+  __shared__ double s_mean[2];
+  __shared__ int s_flag;
+  const int n = (int)(__ldg(cutk) >> 32);
+  double ax = 0.0, ay = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x)
+  {
+    const double2 xy = *reinterpret_cast<const double2 *>(set + i);
+    ax += xy.x;
+    ay += xy.y;
+  }
+  const double tx = block_sum(ax, s_red);
+  const double ty = block_sum(ay, s_red);
+  if (threadIdx.x == 0)
+  {
+    s_mean[0] = tx / n;
+    s_mean[1] = ty / n;
+    s_flag = 0;
+  }
+  __syncthreads();
+  const double mx = s_mean[0], my = s_mean[1];
+  for (int i = threadIdx.x; i < n; i += blockDim.x)
+  {
+    const double2 xy = *reinterpret_cast<const double2 *>(set + i);
+    if (fabs(xy.x - mx) > thr || fabs(xy.y - my) > thr) s_flag = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) out[0] = s_flag;
+}
+
+// Filters up to this many samples take the single-trip path of run_resample.
+constexpr int kSmallFilter = 16384;
+constexpr int kSmallHeadPinned = 4;    // clusters whose sums ride along in the pinned scalar block
+
 // ------------------------------------------------------------------- launchers --
 
 static inline int blocks_for(int n, int threads) { return n > 0 ? (n + threads - 1) / threads : 1; }
@@ -1220,6 +1281,7 @@ static BinTable table_of(const PfCtx *c)
   T.dense = c->tab_dense;
   T.x0 = c->tab_lo[0]; T.y0 = c->tab_lo[1]; T.t0 = c->tab_lo[2];
   T.ex = c->tab_ext[0]; T.ey = c->tab_ext[1]; T.et = c->tab_ext[2];
+  T.n_dev = nullptr;
   return T;
 }
 
@@ -1258,6 +1320,8 @@ static void build_histogram(PfCtx *c, int count)
   mark_first<<<blocks_for(count, 256), 256, 0, st>>>(c->d_tab_first, c->d_slot, 0, count, c->d_flag);
   AMCL_LAUNCH_CHECK();
 }
+
+static void publish_clusters(pf_sample_set_t *set, const double *acc, int ncl);
 
 // Labels + statistics for samples [0, n) of set `which`; the histogram
 // (d_slot and the bin table) must describe at least those samples.
@@ -1379,7 +1443,13 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
   AMCL_CUDA(cudaMemcpyAsync(acc.data(), c->d_cluster_acc, sizeof(double) * 10 * (size_t)ncl,
                             cudaMemcpyDeviceToHost, st));
   AMCL_CUDA(cudaStreamSynchronize(st));
+  publish_clusters(set, acc.data(), ncl);
+}
 
+// pf.c:576-693 on the host: the per-cluster sums [count, w, w x, w y, w cos, w sin,
+// w xx, w xy, w yx, w yy] become pf_cluster_t entries and the set's mean / covariance.
+static void publish_clusters(pf_sample_set_t *set, const double *acc, int ncl)
+{
   // pf.c:576-589 zeroes every slot; here only the ones that were in use
   const int prev = set->cluster_count;
   int limit = ncl < set->cluster_max_count ? ncl : set->cluster_max_count;
@@ -1390,7 +1460,7 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
   double m[4] = {0, 0, 0, 0}, cc[2][2] = {{0, 0}, {0, 0}}, weight = 0.0;
   for (int k = 0; k < ncl; k++)
   {
-    const double *a = acc.data() + (size_t)10 * k;
+    const double *a = acc + (size_t)10 * k;
     weight += a[1];
     for (int q = 0; q < 4; q++) m[q] += a[2 + q];
     cc[0][0] += a[6]; cc[0][1] += a[7]; cc[1][0] += a[8]; cc[1][1] += a[9];
@@ -1525,6 +1595,127 @@ void run_copy_set(PfCtx *c, int from, int to)
   pf->sets[to].sample_count = n;
   pf->sets[to].converged = pf->sets[from].converged;
   c->host_fresh[to] = false;
+}
+
+// The tail of pf_update_resample for a small, unsharded filter: histogram, cut,
+// weights, labels, statistics and convergence without the host in between.
+static void resample_small_tail(PfCtx *c, int ia, int ib, int maxs, bool host_stream, double w_diff,
+                                unsigned short saved_state[3], Particle *d_injected, int *d_inject_slot,
+                                Trace &tr)
+{
+  (void)ia;
+  cudaStream_t st = globals().stream;
+  pf_t *pf = c->host;
+  pf_sample_set_t *set_b = pf->sets + ib;
+  c->tab_dense = 0;
+  AMCL_CUDA(cudaMemsetAsync(c->d_tab_key, 0xFF, sizeof(unsigned long long) * (size_t)c->hash_cap, st));
+  AMCL_CUDA(cudaMemsetAsync(c->d_tab_first, 0xFF, sizeof(unsigned int) * (size_t)c->hash_cap, st));
+  BinTable T = table_of(c);
+  bin_insert<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_keys, 0, maxs, T, c->d_slot);
+  AMCL_LAUNCH_CHECK();
+  mark_first<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_tab_first, c->d_slot, 0, maxs, c->d_flag);
+  AMCL_LAUNCH_CHECK();
+  scan_u32(c, c->d_flag, c->d_scan, maxs, I_DISTINCT);
+  unsigned long long *d_cutk = reinterpret_cast<unsigned long long *>(c->d_ints + I_CUTK);
+  AMCL_CUDA(cudaMemsetAsync(d_cutk, 0x7F, sizeof(unsigned long long), st));
+  find_kld_cut<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_scan, 0, maxs, nullptr, 0, pf->min_samples, maxs,
+                                                      pf->pop_err, pf->pop_z, d_cutk);
+  AMCL_LAUNCH_CHECK();
+  set_uniform_weight_dev<<<blocks_for(maxs, 256), 256, 0, st>>>(c->d_set[ib], maxs, d_cutk);
+  AMCL_LAUNCH_CHECK();
+  // labels of the occupied bins among the first n samples
+  T.n_dev = d_cutk;
+  unsigned int *cmin = c->d_scan + c->alloc_samples;
+  const unsigned int nslots = c->hash_cap;
+  const int sb = (int)((nslots + 255u) / 256u);
+  cc_init<<<sb, 256, 0, st>>>(T, nslots, 0, cmin);
+  AMCL_LAUNCH_CHECK();
+  cc_link<<<sb, 256, 0, st>>>(T, nslots, 0);
+  AMCL_LAUNCH_CHECK();
+  cc_flatten<<<sb, 256, 0, st>>>(T, nslots, 0);
+  AMCL_LAUNCH_CHECK();
+  cc_component_min<<<sb, 256, 0, st>>>(T, nslots, 0, cmin);
+  AMCL_LAUNCH_CHECK();
+  if (!c->d_rootlist) AMCL_CUDA(cudaMalloc(&c->d_rootlist, sizeof(unsigned int) * 2 * kRootListCap));
+  AMCL_CUDA(cudaMemsetAsync(c->d_ints + I_CLUSTERS, 0, sizeof(int), st));
+  cc_collect_roots<<<sb, 256, 0, st>>>(T, nslots, 0, cmin, c->d_rootlist, c->d_rootlist + kRootListCap,
+                                       c->d_ints + I_CLUSTERS);
+  AMCL_LAUNCH_CHECK();
+  cc_rank_roots<<<kRootListCap / 256, 256, 0, st>>>(c->d_rootlist, c->d_rootlist + kRootListCap, 0, cmin,
+                                                    c->d_ints + I_CLUSTERS);
+  AMCL_LAUNCH_CHECK();
+  // Should there be more clusters than the short list ranks, a root keeps its
+  // earliest sample index (< maxs) as label: room for that many rows keeps the
+  // sums in bounds; they are thrown away and redone the long way below.
+  const int acc_rows = maxs + 1;
+  if (acc_rows > c->cluster_acc_cap)
+  {
+    if (c->d_cluster_acc) cudaFree(c->d_cluster_acc);
+    c->cluster_acc_cap = acc_rows + 64;
+    AMCL_CUDA(cudaMalloc(&c->d_cluster_acc, sizeof(double) * 10 * (size_t)c->cluster_acc_cap));
+  }
+  const int zero_rows = acc_rows < kRootListCap ? acc_rows : kRootListCap;
+  AMCL_CUDA(cudaMemsetAsync(c->d_cluster_acc, 0, sizeof(double) * 10 * (size_t)zero_rows, st));
+  {
+    int grid = globals().sm_count * 8;
+    if (grid > blocks_for(maxs, 256)) grid = blocks_for(maxs, 256);
+    cluster_accumulate<<<grid, 256, 0, st>>>(c->d_set[ib], maxs, c->d_tab_aux, c->d_slot, cmin,
+                                             c->d_cluster_acc, c->d_label, 0, d_cutk);
+    AMCL_LAUNCH_CHECK();
+  }
+  converged_small<<<1, 1024, 0, st>>>(c->d_set[ib], d_cutk, pf->dist_threshold, c->d_ints + I_OUTSIDE);
+  AMCL_LAUNCH_CHECK();
+  // the one trip: ints 0..7 (cluster count, outside flag, the (n, k) pair) and
+  // the sums of the first clusters
+  const int head_rows = kSmallHeadPinned < zero_rows ? kSmallHeadPinned : zero_rows;
+  AMCL_CUDA(cudaMemcpyAsync(c->h_ints, c->d_ints, sizeof(int) * 8, cudaMemcpyDeviceToHost, st));
+  AMCL_CUDA(cudaMemcpyAsync(c->h_scalars + 16, c->d_cluster_acc, sizeof(double) * 10 * (size_t)head_rows,
+                            cudaMemcpyDeviceToHost, st));
+  AMCL_CUDA(cudaStreamSynchronize(st));
+  const unsigned long long cutk = *reinterpret_cast<unsigned long long *>(c->h_ints + I_CUTK);
+  const int n = (int)(cutk >> 32);
+  set_b->sample_count = n;                                      // pf.c:483
+  set_b->kdtree->leaf_count = (int)(cutk & 0xFFFFFFFFull);      // k_{n-1}
+  tr.mark("one trip");
+  if (host_stream)
+  {
+    // leave libc's stream where the reference would have left it
+    seed48(saved_state);
+    for (int m = 0; m < n; m++)
+    {
+      if (drand48() < w_diff) (void)(pf->random_pose_fn)(pf->random_pose_data);
+      else (void)drand48();
+    }
+  }
+  c->draws_used = 2ull * (unsigned long long)n;
+  if (w_diff > 0.0) pf->w_slow = pf->w_fast = 0.0;     // pf.c:487-489
+  c->host_fresh[ib] = false;
+  c->replicated[ib] = true;
+  if (d_injected)
+  {
+    cudaFree(d_injected);
+    cudaFree(d_inject_slot);
+  }
+  const int ncl = c->h_ints[I_CLUSTERS];
+  if (ncl > kRootListCap)
+    cluster_and_stats(c, ib, n);                       // rare: the long way (flag + scan ranking)
+  else if (ncl <= head_rows)
+    publish_clusters(set_b, c->h_scalars + 16, ncl);
+  else
+  {
+    static std::vector<double> all;
+    all.resize((size_t)10 * ncl);
+    AMCL_CUDA(cudaMemcpyAsync(all.data(), c->d_cluster_acc, sizeof(double) * 10 * (size_t)ncl,
+                              cudaMemcpyDeviceToHost, st));
+    AMCL_CUDA(cudaStreamSynchronize(st));
+    publish_clusters(set_b, all.data(), ncl);
+  }
+  pf->current_set = ib;
+  const int conv = c->h_ints[I_OUTSIDE] ? 0 : 1;
+  set_b->converged = conv;
+  pf->converged = conv;
+  tr.mark("clusters");
+  tr.report("pf_update_resample (single trip)");
 }
 
 // pf_update_resample (pf.c:363-510)
@@ -1754,6 +1945,19 @@ void run_resample(PfCtx *c)
   pick_and_copy<<<blocks_for(pa.count, 256), 256, 0, st>>>(pa);
   AMCL_LAUNCH_CHECK();
   tr.mark("pick+keys");
+
+  // ---- node-sized filters: everything below in ONE trip to the host -----------
+  // (amcl_node runs 500 .. 10 000 particles; at that size the update is launch
+  // and synchronisation latency, not work.)  The histogram is always the hash --
+  // no bounding box to fetch --, the cut (n, k) stays on the device and the
+  // kernels after it read n from there; the host gets n, k, the cluster count,
+  // the convergence flag and the first clusters' sums in a single copy.
+  if (!sh.on() && maxs <= kSmallFilter)
+  {
+    resample_small_tail(c, ia, ib, maxs, host_stream, w_diff, saved_state, d_injected, d_inject_slot, tr);
+    return;
+  }
+
   // ---- histogram, k_m, KLD cut ---------------------------------------------
   // The KLD count is a property of the global sample ORDER: k_m = number of
   // distinct bins among samples 0..m.
