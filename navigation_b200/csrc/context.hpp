@@ -162,6 +162,14 @@ void nccl_allreduce(void *comm, void *d_buf, int count, int dtype, int op);
 void nccl_allgather(void *comm, int rank, void *d_buf, unsigned long long bytes_per_rank);
 void nccl_release(void *comm);
 
+// The captured launch chain of the small-filter resampling tail (resample_dev.cu).
+struct SmallGraph
+{
+  cudaGraphExec_t exec = nullptr;
+  double key[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // what the captured arguments depend on
+  int launches = 0;                           // kernels inside, for amclb200_launch_count
+};
+
 struct PfCtx
 {
   pf_t *host = nullptr;
@@ -245,6 +253,8 @@ struct PfCtx
   bool stage_pending[3] = {false, false, false};
   float ms_sensor_kernel = 0;     // the laser-model kernel alone
   bool sensor_kernel_pending = false;  // ev_a / ev_b recorded, not read yet
+  SmallGraph small_graph[2];      // one per destination set
+  cudaStream_t capture_stream = nullptr;
   bool defer_total = false;       // pf_update_sensor is calling one of the library's own models: the
                                   // total weight stays on the device until the normalisation reads it
   long long sensor_evals = 0;     // particle-beam evaluations of that launch

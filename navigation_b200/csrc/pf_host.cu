@@ -107,6 +107,9 @@ void pf_ctx_release(pf_t *pf)
   for (int j = 0; j < 2; j++) if (c->d_peer_tab[j]) cudaFree((void *)c->d_peer_tab[j]);
   if (c->d_wpack) cudaFree(c->d_wpack);
   if (c->shard.nccl_comm) nccl_release(c->shard.nccl_comm);
+  for (int j = 0; j < 2; j++)
+    if (c->small_graph[j].exec) cudaGraphExecDestroy(c->small_graph[j].exec);
+  if (c->capture_stream) cudaStreamDestroy(c->capture_stream);
   for (int k = 0; k < 3; k++)
     for (int j = 0; j < 2; j++)
       if (c->ev_stage[k][j]) cudaEventDestroy(c->ev_stage[k][j]);

@@ -1597,17 +1597,12 @@ void run_copy_set(PfCtx *c, int from, int to)
   c->host_fresh[to] = false;
 }
 
-// The tail of pf_update_resample for a small, unsharded filter: histogram, cut,
-// weights, labels, statistics and convergence without the host in between.
-static void resample_small_tail(PfCtx *c, int ia, int ib, int maxs, bool host_stream, double w_diff,
-                                unsigned short saved_state[3], Particle *d_injected, int *d_inject_slot,
-                                Trace &tr)
+// Everything the small tail puts on the stream, and nothing else (no allocation,
+// no wait): this is what is captured into a CUDA graph.
+static void small_tail_enqueue(PfCtx *c, int ib, int maxs)
 {
-  (void)ia;
   cudaStream_t st = globals().stream;
   pf_t *pf = c->host;
-  pf_sample_set_t *set_b = pf->sets + ib;
-  c->tab_dense = 0;
   AMCL_CUDA(cudaMemsetAsync(c->d_tab_key, 0xFF, sizeof(unsigned long long) * (size_t)c->hash_cap, st));
   AMCL_CUDA(cudaMemsetAsync(c->d_tab_first, 0xFF, sizeof(unsigned int) * (size_t)c->hash_cap, st));
   BinTable T = table_of(c);
@@ -1636,7 +1631,6 @@ static void resample_small_tail(PfCtx *c, int ia, int ib, int maxs, bool host_st
   AMCL_LAUNCH_CHECK();
   cc_component_min<<<sb, 256, 0, st>>>(T, nslots, 0, cmin);
   AMCL_LAUNCH_CHECK();
-  if (!c->d_rootlist) AMCL_CUDA(cudaMalloc(&c->d_rootlist, sizeof(unsigned int) * 2 * kRootListCap));
   AMCL_CUDA(cudaMemsetAsync(c->d_ints + I_CLUSTERS, 0, sizeof(int), st));
   cc_collect_roots<<<sb, 256, 0, st>>>(T, nslots, 0, cmin, c->d_rootlist, c->d_rootlist + kRootListCap,
                                        c->d_ints + I_CLUSTERS);
@@ -1648,12 +1642,6 @@ static void resample_small_tail(PfCtx *c, int ia, int ib, int maxs, bool host_st
   // earliest sample index (< maxs) as label: room for that many rows keeps the
   // sums in bounds; they are thrown away and redone the long way below.
   const int acc_rows = maxs + 1;
-  if (acc_rows > c->cluster_acc_cap)
-  {
-    if (c->d_cluster_acc) cudaFree(c->d_cluster_acc);
-    c->cluster_acc_cap = acc_rows + 64;
-    AMCL_CUDA(cudaMalloc(&c->d_cluster_acc, sizeof(double) * 10 * (size_t)c->cluster_acc_cap));
-  }
   const int zero_rows = acc_rows < kRootListCap ? acc_rows : kRootListCap;
   AMCL_CUDA(cudaMemsetAsync(c->d_cluster_acc, 0, sizeof(double) * 10 * (size_t)zero_rows, st));
   {
@@ -1671,6 +1659,64 @@ static void resample_small_tail(PfCtx *c, int ia, int ib, int maxs, bool host_st
   AMCL_CUDA(cudaMemcpyAsync(c->h_ints, c->d_ints, sizeof(int) * 8, cudaMemcpyDeviceToHost, st));
   AMCL_CUDA(cudaMemcpyAsync(c->h_scalars + 16, c->d_cluster_acc, sizeof(double) * 10 * (size_t)head_rows,
                             cudaMemcpyDeviceToHost, st));
+}
+
+// The tail of pf_update_resample for a small, unsharded filter: histogram, cut,
+// weights, labels, statistics and convergence without the host in between.
+static void resample_small_tail(PfCtx *c, int ia, int ib, int maxs, bool host_stream, double w_diff,
+                                unsigned short saved_state[3], Particle *d_injected, int *d_inject_slot,
+                                Trace &tr)
+{
+  (void)ia;
+  cudaStream_t st = globals().stream;
+  pf_t *pf = c->host;
+  pf_sample_set_t *set_b = pf->sets + ib;
+  c->tab_dense = 0;        // the histogram of this path is always the hash
+  // buffers the chain needs, made before anything is captured
+  if (!c->d_rootlist) AMCL_CUDA(cudaMalloc(&c->d_rootlist, sizeof(unsigned int) * 2 * kRootListCap));
+  const int acc_rows = maxs + 1;
+  if (acc_rows > c->cluster_acc_cap)
+  {
+    if (c->d_cluster_acc) cudaFree(c->d_cluster_acc);
+    c->cluster_acc_cap = acc_rows + 64;
+    AMCL_CUDA(cudaMalloc(&c->d_cluster_acc, sizeof(double) * 10 * (size_t)c->cluster_acc_cap));
+  }
+  const int zero_rows = acc_rows < kRootListCap ? acc_rows : kRootListCap;
+  const int head_rows = kSmallHeadPinned < zero_rows ? kSmallHeadPinned : zero_rows;
+  // The chain is ~20 tiny launches with fixed arguments: replayed as ONE graph
+  // launch.  It is captured again whenever something it has baked in changes
+  // (the caller may poke pop_err / pop_z / dist_threshold between updates).
+  SmallGraph &g = c->small_graph[ib];
+  const double key[8] = {(double)maxs, (double)pf->min_samples, pf->pop_err, pf->pop_z, pf->dist_threshold,
+                         (double)c->cluster_acc_cap, (double)(size_t)c->d_cluster_acc,
+                         (double)set_b->kdtree->size[0] + 1e3 * set_b->kdtree->size[1] + 1e6 * set_b->kdtree->size[2]};
+  static const bool use_graph = !(getenv("AMCLB200_NO_GRAPH") && getenv("AMCLB200_NO_GRAPH")[0] == '1');
+  if (use_graph && !amcl_debug_sync())
+  {
+    if (!g.exec || memcmp(key, g.key, sizeof(key)) != 0)
+    {
+      if (g.exec) cudaGraphExecDestroy(g.exec);
+      g.exec = nullptr;
+      if (!c->capture_stream) AMCL_CUDA(cudaStreamCreateWithFlags(&c->capture_stream, cudaStreamNonBlocking));
+      cudaStream_t user_stream = globals().stream;
+      const unsigned long long launches0 = amcl_launch_counter();
+      globals().stream = c->capture_stream;
+      AMCL_CUDA(cudaStreamBeginCapture(c->capture_stream, cudaStreamCaptureModeThreadLocal));
+      small_tail_enqueue(c, ib, maxs);
+      cudaGraph_t graph = nullptr;
+      AMCL_CUDA(cudaStreamEndCapture(c->capture_stream, &graph));
+      globals().stream = user_stream;
+      AMCL_CUDA(cudaGraphInstantiate(&g.exec, graph, 0));
+      cudaGraphDestroy(graph);
+      g.launches = (int)(amcl_launch_counter() - launches0);
+      amcl_launch_counter() = launches0;
+      memcpy(g.key, key, sizeof(key));
+    }
+    AMCL_CUDA(cudaGraphLaunch(g.exec, st));
+    amcl_launch_counter() += (unsigned long long)g.launches;
+  }
+  else
+    small_tail_enqueue(c, ib, maxs);
   AMCL_CUDA(cudaStreamSynchronize(st));
   const unsigned long long cutk = *reinterpret_cast<unsigned long long *>(c->h_ints + I_CUTK);
   const int n = (int)(cutk >> 32);
