@@ -281,7 +281,8 @@ __global__ void cs_tile_fns(const Weights W, int n, const int *__restrict__ tile
 // clean sub-tile its function, one thread chains the sub-tiles in integer
 // arithmetic (converting only where the binade changes) and walks the few dirty
 // ones, then the warps write the entries.
-constexpr int kSubTile = 32;
+constexpr int kSubPer = 2;                     // weights per lane
+constexpr int kSubTile = 32 * kSubPer;         // weights per sub-tile (one warp pass)
 
 struct SubScratch           // shared memory for up to MAXT sub-tiles
 {
@@ -301,10 +302,22 @@ __device__ __forceinline__ double pow2(int e)          // 2^e, |e| < 1022
   return __longlong_as_double((long long)(1023 + e) << 52);
 }
 
+// Inclusive warp scan of a lane's composed function (lane order = element order).
+__device__ __forceinline__ PairFn warp_scan_fn(PairFn inc, int lane)
+{
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1)
+  {
+    const PairFn up = fn_shfl_up(inc, o);
+    if (lane >= o) inc = fn_compose(up, inc);
+  }
+  return inc;
+}
+
 // s_w[0..m): the weights; carry0: the table entry in front of them; n_total: the
 // length of the whole table (error margin of the rough prefix); out[k + 1] receives
-// the entry behind weight k.  All threads of the block must call; the carry out is
-// returned to all of them.
+// the entry behind weight k.  All threads of the block must call (at most
+// blockDim.x sub-tiles); the carry out is returned to all of them.
 __device__ double block_exact_table(const double *s_w, int m, double carry0, int n_total,
                                     double *__restrict__ out, const SubScratch S)
 {
@@ -313,9 +326,15 @@ __device__ double block_exact_table(const double *s_w, int m, double carry0, int
   // A: sum and maximum of every sub-tile
   for (int t = warp; t < tiles; t += nwarps)
   {
-    const int i = t * kSubTile + lane;
-    const double w = i < m ? s_w[i] : 0.0;
-    double v = w, mx = w;
+    double v = 0.0, mx = 0.0;
+#pragma unroll
+    for (int q = 0; q < kSubPer; q++)
+    {
+      const int i = t * kSubTile + lane * kSubPer + q;
+      const double w = i < m ? s_w[i] : 0.0;
+      v += w;
+      mx = fmax(mx, w);
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1)
     {
@@ -325,25 +344,37 @@ __device__ double block_exact_table(const double *s_w, int m, double carry0, int
     if (lane == 0) { S.tsum[t] = v; S.tmax[t] = mx; }
   }
   __syncthreads();
-  // B: rough prefix and classification (the margins of cs_classify)
-  if (tid == 0)
+  // B: rough prefix (block scan, one sub-tile per thread) and classification with
+  // the margins of cs_classify
   {
-    const double eps = 4.0 * (double)n_total * 1.1102230246251565e-16;
-    double run = carry0;
-    for (int t = 0; t < tiles; t++)
+    const double v = tid < tiles ? S.tsum[tid] : 0.0;
+    double inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
     {
-      const double start = run * (1.0 - eps);
-      run += S.tsum[t];
-      const double end = run * (1.0 + eps);
+      const double up = __shfl_up_sync(kFullMask, inc, o);
+      if (lane >= o) inc += up;
+    }
+    if (lane == 31 && warp * 32 < tiles) S.cin[warp] = inc;   // warp totals (cin is free until step D)
+    __syncthreads();
+    double base = carry0;
+    if (tid < tiles)
+      for (int w = 0; w < warp; w++) base += S.cin[w];
+    __syncthreads();
+    if (tid < tiles)
+    {
+      const double eps = 4.0 * (double)n_total * 1.1102230246251565e-16;
+      const double start = (base + (inc - v)) * (1.0 - eps);
+      const double end = (base + inc) * (1.0 + eps);
       int cls = kDirty;
-      if (S.tsum[t] == 0.0 || (start > 0.0 && S.tmax[t] < start * 2.7755575615628914e-17))
+      if (v == 0.0 || (start > 0.0 && S.tmax[tid] < start * 2.7755575615628914e-17))
         cls = kFlat;
       else if (start > 0.0 && end < 1.0e300)
       {
         const int e0 = exponent_of(start), e1 = exponent_of(end);
         if (e0 == e1 && e0 > -1020 && e0 < 1020) cls = e0;
       }
-      S.cls[t] = cls;
+      S.cls[tid] = cls;
     }
   }
   __syncthreads();
@@ -352,15 +383,15 @@ __device__ double block_exact_table(const double *s_w, int m, double carry0, int
   {
     const int cls = S.cls[t];
     if (cls == kDirty || cls == kFlat) continue;            // uniform across the warp
-    const int i = t * kSubTile + lane;
-    PairFn inc = i < m ? fn_of_weight(s_w[i], 52 - cls) : fn_identity();
+    PairFn f = fn_identity();
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1)
+    for (int q = 0; q < kSubPer; q++)
     {
-      const PairFn up = fn_shfl_up(inc, o);
-      if (lane >= o) inc = fn_compose(up, inc);
+      const int i = t * kSubTile + lane * kSubPer + q;
+      if (i < m) f = fn_compose(f, fn_of_weight(s_w[i], 52 - cls));
     }
-    if (lane == 31) S.fn[t] = inc;
+    f = warp_scan_fn(f, lane);
+    if (lane == 31) S.fn[t] = f;
   }
   __syncthreads();
   // D: the exact carry into every sub-tile; dirty ones are walked here
@@ -370,9 +401,17 @@ __device__ double block_exact_table(const double *s_w, int m, double carry0, int
     unsigned long long C = 0ull;
     int e = 0;
     bool as_int = false;
+    int cls_next = tiles > 0 ? S.cls[0] : kFlat;
+    PairFn fn_next = tiles > 0 ? S.fn[0] : fn_identity();
     for (int t = 0; t < tiles; t++)
     {
-      const int cls = S.cls[t];
+      const int cls = cls_next;
+      const PairFn fn = fn_next;
+      if (t + 1 < tiles)                     // fetched a round early: this loop is all latency
+      {
+        cls_next = S.cls[t + 1];
+        fn_next = S.fn[t + 1];
+      }
       if (cls != kDirty && cls != kFlat)
       {
         if (!as_int || e != cls)
@@ -383,7 +422,7 @@ __device__ double block_exact_table(const double *s_w, int m, double carry0, int
           as_int = true;
         }
         S.cin_int[t] = C;
-        C = fn_apply(S.fn[t], C);
+        C = fn_apply(fn, C);
         continue;
       }
       if (as_int)
@@ -411,21 +450,34 @@ __device__ double block_exact_table(const double *s_w, int m, double carry0, int
   {
     const int cls = S.cls[t];
     if (cls == kDirty) continue;
-    const int i = t * kSubTile + lane;
+    const int i0 = t * kSubTile + lane * kSubPer;
     if (cls == kFlat)
     {
-      if (i < m) out[i + 1] = S.cin[t];
+#pragma unroll
+      for (int q = 0; q < kSubPer; q++)
+        if (i0 + q < m) out[i0 + q + 1] = S.cin[t];
       continue;
     }
     const int shift = 52 - cls;
-    PairFn inc = i < m ? fn_of_weight(s_w[i], shift) : fn_identity();
+    PairFn mine[kSubPer];
+    PairFn f = fn_identity();
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1)
+    for (int q = 0; q < kSubPer; q++)
     {
-      const PairFn up = fn_shfl_up(inc, o);
-      if (lane >= o) inc = fn_compose(up, inc);
+      mine[q] = i0 + q < m ? fn_of_weight(s_w[i0 + q], shift) : fn_identity();
+      f = fn_compose(f, mine[q]);
     }
-    if (i < m) out[i + 1] = (double)fn_apply(inc, S.cin_int[t]) * pow2(-shift);
+    const PairFn inc = warp_scan_fn(f, lane);
+    PairFn ex = fn_shfl_up(inc, 1);
+    if (lane == 0) ex = fn_identity();
+    unsigned long long C = fn_apply(ex, S.cin_int[t]);
+    const double unit = pow2(-shift);
+#pragma unroll
+    for (int q = 0; q < kSubPer; q++)
+    {
+      C = fn_apply(mine[q], C);
+      if (i0 + q < m) out[i0 + q + 1] = (double)C * unit;
+    }
   }
   const double result = S.carry[0];
   __syncthreads();
@@ -610,7 +662,7 @@ __global__ void cs_verify(const Weights W, int n, const double *__restrict__ cum
 }
 
 // ---- node-sized filters: the whole table in one launch, nothing returns to the host ---
-constexpr int kSmallMaxTiles = 512;                       // n <= 16384
+constexpr int kSmallMaxTiles = 16384 / kSubTile;          // n <= 16384
 __device__ unsigned long long g_small_fallbacks_dev = 0;
 
 __global__ void __launch_bounds__(1024)
