@@ -72,7 +72,7 @@ PfCtx *pf_ctx_create(pf_t *pf)
   const size_t maxs = (size_t)pf->max_samples + kShardPad;
   c->max_samples = pf->max_samples;
   c->alloc_samples = (int)maxs;
-  c->hash_cap = next_pow2((unsigned int)(2 * maxs + 2));
+  c->hash_cap = next_pow2((unsigned int)(2 * (size_t)pf->max_samples + 2));   // bins <= samples: load factor <= 1/2
   for (int j = 0; j < 2; j++) AMCL_CUDA(cudaMalloc(&c->d_set[j], sizeof(Particle) * maxs));
   AMCL_CUDA(cudaMalloc(&c->d_cum, sizeof(double) * (maxs + 1)));
   AMCL_CUDA(cudaMalloc(&c->d_draws, sizeof(double) * 2 * maxs));
