@@ -806,6 +806,12 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int 
   // (bricks_per_owner > 0).  Phase 1 (own bricks only): pairs whose two bricks
   // have the same owner.  Phase 2 (all bricks, after the ranks' forests have been
   // merged): the pairs that straddle owners.  Unsharded: one pass, every pair.
+  //
+  // A warp is 32 x-neighbours of one (y, heading) row of the brick; on a brick
+  // face most of them want to unite the SAME two brick-local trees (after
+  // cc_brick_local, aux[] of a cell is its brick-local root).  Lanes that hold the
+  // same (tree of this cell, tree of the neighbour) pair elect one to do the
+  // union: every pair of trees is united once per warp instead of once per cell.
   const int brick = (int)blockIdx.x + brick_base;
   const int lx = threadIdx.x & (kBrickX - 1);
   const int ly = (threadIdx.x / kBrickX) & (kBrickY - 1);
@@ -814,39 +820,58 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int 
   const int by = (brick / bricks_x) % bricks_y;
   const int bt = brick / (bricks_x * bricks_y);
   const int ix = bx * kBrickX + lx, iy = by * kBrickY + ly, it = bt * kBrickT + lt;
-  if (ix >= T.ex || iy >= T.ey || it >= T.et) return;
+  const unsigned int nv = table_valid(T, n_valid);
+  bool active = ix < T.ex && iy < T.ey && it < T.et;
   // only cells on a forward face (or next to the low-x / low-y face, whose
   // forward neighbours with dx or dy = -1 leave the brick) have work to do
-  if (lx != 0 && lx != kBrickX - 1 && ly != 0 && ly != kBrickY - 1 && lt != kBrickT - 1) return;
-  const unsigned int s = (unsigned int)((it * T.ey + iy) * T.ex + ix);
-  if (T.first[s] >= table_valid(T, n_valid)) return;
+  if (lx != 0 && lx != kBrickX - 1 && ly != 0 && ly != kBrickY - 1 && lt != kBrickT - 1) active = false;
+  const unsigned int s = active ? (unsigned int)((it * T.ey + iy) * T.ex + ix) : 0u;
+  if (active && T.first[s] >= nv) active = false;
+  if (__ballot_sync(kFullMask, active) == 0u) return;          // warp-uniform
+  const unsigned int mine = active ? __ldcg(&T.aux[s]) : 0u;   // this cell's tree
   for (int q = 14; q < 27; q++)
   {
     const int dt = q / 9 - 1, dy = (q % 9) / 3 - 1, dx = (q % 9) % 3 - 1;
-    const int mx = lx + dx, my = ly + dy, mt = lt + dt;
-    if ((unsigned)mx < (unsigned)kBrickX && (unsigned)my < (unsigned)kBrickY &&
-        (unsigned)mt < (unsigned)kBrickT)
-      continue;                                   // inside the brick: done locally
+    bool want = active;
+    unsigned int nb = 0u;
+    if (want)
+    {
+      const int mx = lx + dx, my = ly + dy, mt = lt + dt;
+      if ((unsigned)mx < (unsigned)kBrickX && (unsigned)my < (unsigned)kBrickY &&
+          (unsigned)mt < (unsigned)kBrickT)
+        want = false;                               // inside the brick: done locally
+    }
     const int nx = ix + dx, ny = iy + dy, nt = it + dt;
-    if ((unsigned)nx >= (unsigned)T.ex || (unsigned)ny >= (unsigned)T.ey || (unsigned)nt >= (unsigned)T.et)
-      continue;
-    if (bricks_per_owner > 0)
+    if (want && ((unsigned)nx >= (unsigned)T.ex || (unsigned)ny >= (unsigned)T.ey || (unsigned)nt >= (unsigned)T.et))
+      want = false;
+    if (want && bricks_per_owner > 0)
     {
       const int nbrick = ((nt / kBrickT) * bricks_y + ny / kBrickY) * bricks_x + nx / kBrickX;
       const bool same_owner = nbrick / bricks_per_owner == brick / bricks_per_owner;
-      if (same_owner != (phase == 1)) continue;
+      if (same_owner != (phase == 1)) want = false;
     }
-    const unsigned int nb = (unsigned int)((nt * T.ey + ny) * T.ex + nx);
-    if (T.first[nb] >= table_valid(T, n_valid)) continue;
-    // same pruning as in cc_brick_local, now with any cell of the grid in between
-    bool implied = false;
-    if ((dx != 0) + (dy != 0) + (dt != 0) >= 2)
+    if (want)
     {
-      if (dx != 0 && T.first[(nt * T.ey + ny) * T.ex + ix] < table_valid(T, n_valid)) implied = true;
-      if (!implied && dy != 0 && T.first[(nt * T.ey + iy) * T.ex + nx] < table_valid(T, n_valid)) implied = true;
-      if (!implied && dt != 0 && T.first[(it * T.ey + ny) * T.ex + nx] < table_valid(T, n_valid)) implied = true;
+      nb = (unsigned int)((nt * T.ey + ny) * T.ex + nx);
+      if (T.first[nb] >= nv) want = false;
     }
-    if (!implied) uf_union(T.aux, s, nb);
+    if (want && (dx != 0) + (dy != 0) + (dt != 0) >= 2)
+    {
+      // same pruning as in cc_brick_local, now with any cell of the grid in between
+      bool implied = false;
+      if (dx != 0 && T.first[(nt * T.ey + ny) * T.ex + ix] < nv) implied = true;
+      if (!implied && dy != 0 && T.first[(nt * T.ey + iy) * T.ex + nx] < nv) implied = true;
+      if (!implied && dt != 0 && T.first[(it * T.ey + ny) * T.ex + nx] < nv) implied = true;
+      if (implied) want = false;
+    }
+    const unsigned int voters = __ballot_sync(kFullMask, want);
+    if (voters == 0u) continue;
+    if (want)
+    {
+      const unsigned long long pair = ((unsigned long long)mine << 32) | __ldcg(&T.aux[nb]);
+      const unsigned int peers = __match_any_sync(voters, pair);
+      if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) uf_union(T.aux, s, nb);
+    }
   }
 }
 
