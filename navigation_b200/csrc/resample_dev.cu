@@ -821,58 +821,63 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int 
   const int bt = brick / (bricks_x * bricks_y);
   const int ix = bx * kBrickX + lx, iy = by * kBrickY + ly, it = bt * kBrickT + lt;
   const unsigned int nv = table_valid(T, n_valid);
+  // occupancy of the brick and of the one-cell shell its forward neighbours and
+  // the "cells between" can lie in (x, y: -1 .. size; heading: 0 .. size), read
+  // once, in rows, instead of up to four scattered loads per neighbour and cell
+  constexpr int kHX = kBrickX + 2, kHY = kBrickY + 2, kHT = kBrickT + 1;
+  __shared__ unsigned char s_occ[kHX * kHY * kHT];
+  for (int k = threadIdx.x; k < kHX * kHY * kHT; k += blockDim.x)
+  {
+    const int hx = k % kHX - 1, hy = (k / kHX) % kHY - 1, ht = k / (kHX * kHY);
+    const int gx = bx * kBrickX + hx, gy = by * kBrickY + hy, gt = bt * kBrickT + ht;
+    bool o = false;
+    if ((unsigned)gx < (unsigned)T.ex && (unsigned)gy < (unsigned)T.ey && (unsigned)gt < (unsigned)T.et)
+      o = T.first[(gt * T.ey + gy) * T.ex + gx] < nv;
+    s_occ[k] = o ? 1 : 0;
+  }
+  __syncthreads();
+#define AMCL_OCC(x, y, t) s_occ[((t) * kHY + ((y) + 1)) * kHX + ((x) + 1)]
   bool active = ix < T.ex && iy < T.ey && it < T.et;
   // only cells on a forward face (or next to the low-x / low-y face, whose
   // forward neighbours with dx or dy = -1 leave the brick) have work to do
   if (lx != 0 && lx != kBrickX - 1 && ly != 0 && ly != kBrickY - 1 && lt != kBrickT - 1) active = false;
-  const unsigned int s = active ? (unsigned int)((it * T.ey + iy) * T.ex + ix) : 0u;
-  if (active && T.first[s] >= nv) active = false;
+  if (active && !AMCL_OCC(lx, ly, lt)) active = false;
   if (__ballot_sync(kFullMask, active) == 0u) return;          // warp-uniform
+  const unsigned int s = active ? (unsigned int)((it * T.ey + iy) * T.ex + ix) : 0u;
   const unsigned int mine = active ? __ldcg(&T.aux[s]) : 0u;   // this cell's tree
   for (int q = 14; q < 27; q++)
   {
     const int dt = q / 9 - 1, dy = (q % 9) / 3 - 1, dx = (q % 9) % 3 - 1;
+    const int mx = lx + dx, my = ly + dy, mt = lt + dt;
     bool want = active;
-    unsigned int nb = 0u;
-    if (want)
-    {
-      const int mx = lx + dx, my = ly + dy, mt = lt + dt;
-      if ((unsigned)mx < (unsigned)kBrickX && (unsigned)my < (unsigned)kBrickY &&
-          (unsigned)mt < (unsigned)kBrickT)
-        want = false;                               // inside the brick: done locally
-    }
-    const int nx = ix + dx, ny = iy + dy, nt = it + dt;
-    if (want && ((unsigned)nx >= (unsigned)T.ex || (unsigned)ny >= (unsigned)T.ey || (unsigned)nt >= (unsigned)T.et))
-      want = false;
+    if ((unsigned)mx < (unsigned)kBrickX && (unsigned)my < (unsigned)kBrickY && (unsigned)mt < (unsigned)kBrickT)
+      want = false;                                 // inside the brick: done locally
+    if (want && !AMCL_OCC(mx, my, mt)) want = false;   // (cells beyond the grid read as empty)
     if (want && bricks_per_owner > 0)
     {
+      const int nx = ix + dx, ny = iy + dy, nt = it + dt;
       const int nbrick = ((nt / kBrickT) * bricks_y + ny / kBrickY) * bricks_x + nx / kBrickX;
       const bool same_owner = nbrick / bricks_per_owner == brick / bricks_per_owner;
       if (same_owner != (phase == 1)) want = false;
     }
-    if (want)
-    {
-      nb = (unsigned int)((nt * T.ey + ny) * T.ex + nx);
-      if (T.first[nb] >= nv) want = false;
-    }
     if (want && (dx != 0) + (dy != 0) + (dt != 0) >= 2)
     {
       // same pruning as in cc_brick_local, now with any cell of the grid in between
-      bool implied = false;
-      if (dx != 0 && T.first[(nt * T.ey + ny) * T.ex + ix] < nv) implied = true;
-      if (!implied && dy != 0 && T.first[(nt * T.ey + iy) * T.ex + nx] < nv) implied = true;
-      if (!implied && dt != 0 && T.first[(it * T.ey + ny) * T.ex + nx] < nv) implied = true;
-      if (implied) want = false;
+      if ((dx != 0 && AMCL_OCC(lx, my, mt)) || (dy != 0 && AMCL_OCC(mx, ly, mt)) ||
+          (dt != 0 && AMCL_OCC(mx, my, lt)))
+        want = false;
     }
     const unsigned int voters = __ballot_sync(kFullMask, want);
     if (voters == 0u) continue;
     if (want)
     {
+      const unsigned int nb = (unsigned int)(((it + dt) * T.ey + (iy + dy)) * T.ex + (ix + dx));
       const unsigned long long pair = ((unsigned long long)mine << 32) | __ldcg(&T.aux[nb]);
       const unsigned int peers = __match_any_sync(voters, pair);
       if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) uf_union(T.aux, s, nb);
     }
   }
+#undef AMCL_OCC
 }
 
 // Every bin follows its parents to the root and points at it directly.  Other
