@@ -188,7 +188,8 @@ struct PfCtx
   bool host_fresh[2] = {false, false};
 
   // resampling scratch
-  double *d_cum = nullptr;        // max+1 cumulative table
+  double *d_cum = nullptr;        // max+1 cumulative table (d_cum + 1 is 256-byte aligned)
+  double *d_cum_raw = nullptr;    // the allocation behind it
   double *d_draws = nullptr;      // 2*max uniforms (u_test, r) of a resample
   double *d_motion_draws = nullptr;  // parity mode: 6 doubles per particle, grown on demand
   int motion_draws_cap = 0;

@@ -74,7 +74,10 @@ PfCtx *pf_ctx_create(pf_t *pf)
   c->alloc_samples = (int)maxs;
   c->hash_cap = next_pow2((unsigned int)(2 * (size_t)pf->max_samples + 2));   // bins <= samples: load factor <= 1/2
   for (int j = 0; j < 2; j++) AMCL_CUDA(cudaMalloc(&c->d_set[j], sizeof(Particle) * maxs));
-  AMCL_CUDA(cudaMalloc(&c->d_cum, sizeof(double) * (maxs + 1)));
+  // entry 0 of the table sits 8 bytes in FRONT of a 256-byte boundary, so that
+  // entries 1.. -- the part a sharded filter all-gathers slice by slice -- are aligned
+  AMCL_CUDA(cudaMalloc(&c->d_cum_raw, sizeof(double) * (maxs + 1 + 32)));
+  c->d_cum = c->d_cum_raw + 31;
   AMCL_CUDA(cudaMalloc(&c->d_draws, sizeof(double) * 2 * maxs));
   AMCL_CUDA(cudaMalloc(&c->d_src, sizeof(int) * maxs));
   AMCL_CUDA(cudaMalloc(&c->d_label, sizeof(int) * maxs));
@@ -113,7 +116,7 @@ void pf_ctx_release(pf_t *pf)
   for (int k = 0; k < 3; k++)
     for (int j = 0; j < 2; j++)
       if (c->ev_stage[k][j]) cudaEventDestroy(c->ev_stage[k][j]);
-  cudaFree(c->d_cum); cudaFree(c->d_draws); cudaFree(c->d_src); cudaFree(c->d_label);
+  cudaFree(c->d_cum_raw); cudaFree(c->d_draws); cudaFree(c->d_src); cudaFree(c->d_label);
   cudaFree(c->d_keys); cudaFree(c->d_slot); cudaFree(c->d_flag); cudaFree(c->d_scan);
   cudaFree(c->d_scan_tiles); cudaFree(c->d_tab_key); cudaFree(c->d_tab_first); cudaFree(c->d_tab_aux); cudaFree(c->d_scalars); cudaFree(c->d_ints);
   if (c->d_cluster_acc) cudaFree(c->d_cluster_acc);
