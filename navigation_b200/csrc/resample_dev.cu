@@ -741,9 +741,13 @@ __device__ __forceinline__ void suf_union(unsigned int *lab, unsigned int a, uns
 }
 
 __global__ void __launch_bounds__(kBrickCells)
-cc_brick_local(const BinTable T, int bricks_x, int bricks_y, int n_valid, unsigned int *cmin, int brick_base)
+cc_brick_local(const BinTable T, int bricks_x, int bricks_y, int n_valid, unsigned int *cmin, int band,
+               int owner)
 {
-  const int brick = (int)blockIdx.x + brick_base;
+  // band > 0 (sharded labelling): rank `owner` labels the bricks of its band of
+  // `band` brick rows along y, every block of another band leaves at once
+  const int brick = (int)blockIdx.x;
+  if (band > 0 && ((brick / bricks_x) % bricks_y) / band != owner) return;
   __shared__ unsigned int s_lab[kBrickCells];
   __shared__ unsigned char s_occ[kBrickCells];
   const int lx = threadIdx.x & (kBrickX - 1);
@@ -799,26 +803,31 @@ cc_brick_local(const BinTable T, int bricks_x, int bricks_y, int n_valid, unsign
 }
 
 __global__ void __launch_bounds__(kBrickCells)
-cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int brick_base,
-                 int bricks_per_owner, int phase)
+cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int band, int owner, int phase)
 {
-  // Sharded labelling splits the bricks into contiguous runs, one per rank
-  // (bricks_per_owner > 0).  Phase 1 (own bricks only): pairs whose two bricks
-  // have the same owner.  Phase 2 (all bricks, after the ranks' forests have been
-  // merged): the pairs that straddle owners.  Unsharded: one pass, every pair.
+  // Sharded labelling gives every rank a band of `band` brick rows along y, all
+  // headings and all x (band > 0): bands only touch on y faces.  Phase 1 (the
+  // rank's own bricks): pairs inside the band.  Phase 2 (after the ranks' forests
+  // have been merged; only the brick rows at a band edge stay): the pairs that
+  // straddle two bands.  Unsharded (band == 0): one pass, every pair.
   //
   // A warp is 32 x-neighbours of one (y, heading) row of the brick; on a brick
   // face most of them want to unite the SAME two brick-local trees (after
   // cc_brick_local, aux[] of a cell is its brick-local root).  Lanes that hold the
   // same (tree of this cell, tree of the neighbour) pair elect one to do the
   // union: every pair of trees is united once per warp instead of once per cell.
-  const int brick = (int)blockIdx.x + brick_base;
+  const int brick = (int)blockIdx.x;
   const int lx = threadIdx.x & (kBrickX - 1);
   const int ly = (threadIdx.x / kBrickX) & (kBrickY - 1);
   const int lt = threadIdx.x / (kBrickX * kBrickY);
   const int bx = brick % bricks_x;
   const int by = (brick / bricks_x) % bricks_y;
   const int bt = brick / (bricks_x * bricks_y);
+  if (band > 0)
+  {
+    if (phase == 1 && by / band != owner) return;                     // block-uniform
+    if (phase == 2 && !((by % band == band - 1 && by + 1 < bricks_y) || (by % band == 0 && by > 0))) return;
+  }
   const int ix = bx * kBrickX + lx, iy = by * kBrickY + ly, it = bt * kBrickT + lt;
   const unsigned int nv = table_valid(T, n_valid);
   // occupancy of the brick and of the one-cell shell its forward neighbours and
@@ -853,11 +862,9 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int 
     if ((unsigned)mx < (unsigned)kBrickX && (unsigned)my < (unsigned)kBrickY && (unsigned)mt < (unsigned)kBrickT)
       want = false;                                 // inside the brick: done locally
     if (want && !AMCL_OCC(mx, my, mt)) want = false;   // (cells beyond the grid read as empty)
-    if (want && bricks_per_owner > 0)
+    if (want && band > 0)
     {
-      const int nx = ix + dx, ny = iy + dy, nt = it + dt;
-      const int nbrick = ((nt / kBrickT) * bricks_y + ny / kBrickY) * bricks_x + nx / kBrickX;
-      const bool same_owner = nbrick / bricks_per_owner == brick / bricks_per_owner;
+      const bool same_owner = ((iy + dy) / kBrickY) / band == by / band;
       if (same_owner != (phase == 1)) want = false;
     }
     if (want && (dx != 0) + (dy != 0) + (dt != 0) >= 2)
@@ -1381,29 +1388,26 @@ static void cluster_and_stats(PfCtx *c, int which, int n)
     const Shard &sh = c->shard;
     if (sh.on() && bricks >= 64 * sh.world)
     {
-      // Every rank labels a contiguous run of bricks; the forests (disjoint sets
-      // of cells, everything else 0xFFFFFFFF = -1) are merged with one MAX
-      // all-reduce; the links between runs are then added by everybody.  Roots
-      // are always the smallest cell index of their tree, so all ranks end up
-      // with identical forests.
-      const int per = (bricks + sh.world - 1) / sh.world;
-      const int b_lo = min(sh.rank * per, bricks), b_hi = min(b_lo + per, bricks);
+      // Every rank labels a band of brick rows along y (all headings, all x);
+      // the forests (disjoint sets of cells, everything else 0xFFFFFFFF = -1) are
+      // merged with one MAX all-reduce; the links between bands -- y faces of the
+      // brick rows at a band edge only -- are then added by everybody.  Roots are
+      // always the smallest cell index of their tree, so all ranks end up with
+      // identical forests.
+      const int band = (byn + sh.world - 1) / sh.world;
       AMCL_CUDA(cudaMemsetAsync(T.aux, 0xFF, sizeof(unsigned int) * (size_t)nslots, st));
       AMCL_CUDA(cudaMemsetAsync(cmin, 0xFF, sizeof(unsigned int) * (size_t)nslots, st));
-      if (b_hi > b_lo)
-      {
-        cc_brick_local<<<b_hi - b_lo, kBrickCells, 0, st>>>(T, bxn, byn, n, cmin, b_lo);
-        AMCL_LAUNCH_CHECK();
-        cc_brick_borders<<<b_hi - b_lo, kBrickCells, 0, st>>>(T, bxn, byn, n, b_lo, per, 1);
-        AMCL_LAUNCH_CHECK();
-      }
+      cc_brick_local<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, cmin, band, sh.rank);
+      AMCL_LAUNCH_CHECK();
+      cc_brick_borders<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, band, sh.rank, 1);
+      AMCL_LAUNCH_CHECK();
       sh.allreduce(T.aux, (int)nslots, SHARD_I32, SHARD_MAX, sh.user);
-      cc_brick_borders<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, 0, per, 2);
+      cc_brick_borders<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, band, sh.rank, 2);
       AMCL_LAUNCH_CHECK();
     }
     else
     {
-      cc_brick_local<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, cmin, 0);
+      cc_brick_local<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, cmin, 0, 0);
       AMCL_LAUNCH_CHECK();
       cc_brick_borders<<<bricks, kBrickCells, 0, st>>>(T, bxn, byn, n, 0, 0, 0);
       AMCL_LAUNCH_CHECK();
