@@ -1,5 +1,5 @@
 """Times the other BASELINE.json configurations (K1-K4) on one B200 and writes
-profiles/configs_r1.json.  bench.py carries the headline (K5); these are the
+profiles/configs_r2.json.  bench.py carries the headline (K5); these are the
 parity-test shapes, timed here so their kernels have numbers too.
 
     python profiles/run_configs.py            # on the GPU box
@@ -151,7 +151,7 @@ def main():
                                "lfp", resample=True))
     res.append(sensor_case("K4t tracking cloud lfp + resample 4M x 1080", 4000, 1 << 22, 1080, "lfp",
                            cloud_kind="tracking", resample=True))
-    out = os.path.join(ROOT, "gpurun_out", "configs_r1.json")
+    out = os.path.join(ROOT, "gpurun_out", "configs_r2.json")
     os.makedirs(os.path.dirname(out), exist_ok=True)
     json.dump(res, open(out, "w"), indent=1)
     for r in res:
