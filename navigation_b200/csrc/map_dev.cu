@@ -498,7 +498,13 @@ __global__ void build_laser_view(const uint16_t *__restrict__ code, int tiles_x,
 #pragma unroll
     for (int k = 0; k < 16; k++) v[k] = (uint16_t)off_rank;
   }
-  uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)t * 16);
+#ifdef AMCL_LF_BLOCK8
+  // 2 x 2 tiles (8 x 8 cells) share a 128-byte line: see lf_index in sensor_dev.cu
+  const size_t at = (size_t)((4 * tj) & ~7) * w + 16 * (size_t)ti + 4 * (size_t)((4 * ti) & ~7) + 8 * (size_t)((4 * tj) & 4);
+#else
+  const size_t at = (size_t)t * 16;
+#endif
+  uint4 *dst = reinterpret_cast<uint4 *>(out + at);
   dst[0] = *reinterpret_cast<const uint4 *>(v);
   dst[1] = *reinterpret_cast<const uint4 *>(v + 8);
 }
@@ -515,7 +521,7 @@ void map_prepare_laser_view(MapCtx *m, int reach_cells)
   while (want > 4 && (size_t)(m->sx + 2 * want) * (size_t)(m->sy + 2 * want) > budget) want -= 4;
   if (m->lf_generation == m->generation && m->lf_apron >= want) return;
   const int apron = want > m->lf_apron ? want : m->lf_apron;
-  const int w = (m->sx + 2 * apron + 3) & ~3, h = (m->sy + 2 * apron + 3) & ~3;
+  const int w = (m->sx + 2 * apron + 7) & ~7, h = (m->sy + 2 * apron + 7) & ~7;
   const size_t elems = (size_t)w * h;
   if (elems > m->lf_cap)
   {

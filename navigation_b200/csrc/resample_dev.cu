@@ -851,10 +851,19 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int 
   // forward neighbours with dx or dy = -1 leave the brick) have work to do
   if (lx != 0 && lx != kBrickX - 1 && ly != 0 && ly != kBrickY - 1 && lt != kBrickT - 1) active = false;
   if (active && !AMCL_OCC(lx, ly, lt)) active = false;
-  if (__ballot_sync(kFullMask, active) == 0u) return;          // warp-uniform
+  // Pairs of trees to unite are first collected per BLOCK (a brick has a handful
+  // of local trees and so have its neighbours: ~10 distinct pairs, against ~150
+  // warp-level candidates), then united once each: the unions are chains of
+  // dependent L2 round trips on a few hot roots, their count is what costs.
+  constexpr int kPairSlots = 256;
+  __shared__ unsigned long long s_pair[kPairSlots];
+  __shared__ uint2 s_pair_cells[kPairSlots];
+  for (int k = threadIdx.x; k < kPairSlots; k += blockDim.x) s_pair[k] = ~0ull;
+  __syncthreads();
   const unsigned int s = active ? (unsigned int)((it * T.ey + iy) * T.ex + ix) : 0u;
   const unsigned int mine = active ? __ldcg(&T.aux[s]) : 0u;   // this cell's tree
-  for (int q = 14; q < 27; q++)
+  const bool warp_has_work = __ballot_sync(kFullMask, active) != 0u;
+  for (int q = 14; warp_has_work && q < 27; q++)
   {
     const int dt = q / 9 - 1, dy = (q % 9) / 3 - 1, dx = (q % 9) % 3 - 1;
     const int mx = lx + dx, my = ly + dy, mt = lt + dt;
@@ -881,10 +890,30 @@ cc_brick_borders(const BinTable T, int bricks_x, int bricks_y, int n_valid, int 
       const unsigned int nb = (unsigned int)(((it + dt) * T.ey + (iy + dy)) * T.ex + (ix + dx));
       const unsigned long long pair = ((unsigned long long)mine << 32) | __ldcg(&T.aux[nb]);
       const unsigned int peers = __match_any_sync(voters, pair);
-      if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) uf_union(T.aux, s, nb);
+      if ((int)(threadIdx.x & 31) == __ffs(peers) - 1)
+      {
+        // enter the pair into the block's set; a full set falls back to uniting at once
+        unsigned int h = (unsigned int)((pair * 0x9E3779B97F4A7C15ull) >> 56);   // 0..255
+        bool placed = false;
+        for (int probe = 0; probe < 16 && !placed; probe++, h = (h + 1) & (kPairSlots - 1))
+        {
+          const unsigned long long prev = atomicCAS(&s_pair[h], ~0ull, pair);
+          if (prev == ~0ull)
+          {
+            s_pair_cells[h] = make_uint2(s, nb);
+            placed = true;
+          }
+          else if (prev == pair)
+            placed = true;
+        }
+        if (!placed) uf_union(T.aux, s, nb);
+      }
     }
   }
 #undef AMCL_OCC
+  __syncthreads();
+  for (int k = threadIdx.x; k < kPairSlots; k += blockDim.x)
+    if (s_pair[k] != ~0ull) uf_union(T.aux, s_pair_cells[k].x, s_pair_cells[k].y);
 }
 
 // Every bin follows its parents to the root and points at it directly.  Other
