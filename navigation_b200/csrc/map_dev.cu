@@ -498,13 +498,7 @@ __global__ void build_laser_view(const uint16_t *__restrict__ code, int tiles_x,
 #pragma unroll
     for (int k = 0; k < 16; k++) v[k] = (uint16_t)off_rank;
   }
-#ifdef AMCL_LF_BLOCK8
-  // 2 x 2 tiles (8 x 8 cells) share a 128-byte line: see lf_index in sensor_dev.cu
-  const size_t at = (size_t)((4 * tj) & ~7) * w + 16 * (size_t)ti + 4 * (size_t)((4 * ti) & ~7) + 8 * (size_t)((4 * tj) & 4);
-#else
-  const size_t at = (size_t)t * 16;
-#endif
-  uint4 *dst = reinterpret_cast<uint4 *>(out + at);
+  uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)t * 16);
   dst[0] = *reinterpret_cast<const uint4 *>(v);
   dst[1] = *reinterpret_cast<const uint4 *>(v + 8);
 }

@@ -129,10 +129,7 @@ constexpr int kBlockP = AMCL_LF_BLOCKP;
 // -- one AND, one multiply-add, one shift-add.
 __device__ __forceinline__ unsigned lf_index(unsigned mi, unsigned mj, unsigned k_row)
 {
-#ifdef AMCL_LF_BLOCK8
-  // experiment: 8 x 8-cell blocks per 128-byte line (2 x 2 tiles); k_row = w here
-  return (mj & ~7u) * k_row + (mj & 3u) + ((mj & 4u) << 3) + ((mi + (mi & ~7u)) << 2);
-#endif
+
   return (mj & ~3u) * k_row + mj + (mi << 2);
 }
 
@@ -772,11 +769,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   a.lf = m->d_lf;
   a.max_i = (unsigned)m->lf_w - 1u;
   a.max_j = (unsigned)m->lf_h - 1u;
-#ifdef AMCL_LF_BLOCK8
-  a.k_row = (unsigned)m->lf_w;
-#else
   a.k_row = (unsigned)m->lf_w - 1u;
-#endif
   a.lx = laser_pose[0];
   a.ly = laser_pose[1];
   a.la = laser_pose[2];
