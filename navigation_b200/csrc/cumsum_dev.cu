@@ -781,6 +781,8 @@ bool exact_cumsum_sharded(PfCtx *c, const Particle *set, int n, double *d_cum)
   PairFn *tile_fn = reinterpret_cast<PairFn *>(c->d_tile_fn);
   if (!c->d_wpack) AMCL_CUDA(cudaMalloc(&c->d_wpack, sizeof(double) * (size_t)c->alloc_samples));
   Weights W = weights_of(set);
+  Trace tr;
+  tr.mark("start");
   // tiles beyond this rank's (and beyond the table's end) must not carry stale sums
   AMCL_CUDA(cudaMemsetAsync(c->d_tile_sum + tile0, 0, sizeof(double) * (size_t)chunk_tiles, st));
   AMCL_CUDA(cudaMemsetAsync(c->d_tile_carry + tile0, 0, sizeof(double) * (size_t)chunk_tiles, st));
@@ -793,6 +795,7 @@ bool exact_cumsum_sharded(PfCtx *c, const Particle *set, int n, double *d_cum)
   W.stride = 1;
   sh.allgather(c->d_tile_sum, (unsigned long long)chunk_tiles * sizeof(double));
   sh.allgather(c->d_tile_carry, (unsigned long long)chunk_tiles * sizeof(double));   // the tile maxima
+  tr.mark("sums+2ag");
   const int bad_slot = 8, dirty_slot = 9, overflow_slot = 10;
   AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, 3 * sizeof(int), st));
   cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, c->d_tile_carry, tiles, n, c->d_tile_class,
@@ -810,6 +813,7 @@ bool exact_cumsum_sharded(PfCtx *c, const Particle *set, int n, double *d_cum)
   sh.allgather(tile_fn, (unsigned long long)chunk_tiles * sizeof(PairFn));
   // rows of tiles this rank does not own are zero here: the sum is a gather
   sh.allreduce(c->d_dirty_w, kMaxDirtyRows * kTileLen, SHARD_F64, SHARD_SUM);
+  tr.mark("classify+fns+ag+ar");
   cs_carries<<<1, 1024, 0, st>>>(W, n, tiles, c->d_tile_class, tile_fn, c->d_tile_carry, d_cum,
                                 c->d_dirty_w, c->d_dirty_row);
   AMCL_LAUNCH_CHECK();
@@ -822,13 +826,17 @@ bool exact_cumsum_sharded(PfCtx *c, const Particle *set, int n, double *d_cum)
     cs_verify<<<(count + 255) / 256, 256, 0, st>>>(W, n, d_cum, c->d_ints + bad_slot, first, count);
     AMCL_LAUNCH_CHECK();
   }
+  tr.mark("carries+apply");
   // entry i + 1 of the table belongs to the owner of weight i
   sh.allgather(d_cum + 1, (unsigned long long)chunk * sizeof(double));
+  tr.mark("ag table");
   // one verdict for everybody: any rank's failed check, or too many dirty tiles
   sh.allreduce(c->d_ints + bad_slot, 3, SHARD_I32, SHARD_MAX);
   AMCL_CUDA(cudaMemcpyAsync(c->h_ints + bad_slot, c->d_ints + bad_slot, 3 * sizeof(int),
                             cudaMemcpyDeviceToHost, st));
   AMCL_CUDA(cudaStreamSynchronize(st));
+  tr.mark("verdict");
+  tr.report("exact_cumsum_sharded");
   g_last_dirty = c->h_ints[dirty_slot];
   g_last_tiles = tiles;
   if (c->h_ints[bad_slot] || c->h_ints[overflow_slot])
