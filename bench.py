@@ -652,6 +652,7 @@ def b200_arm(args):
         "stage_ms": {"action": st_action, "sensor": st_sensor, "resample": st_resample,
                      "edt_kernels": edt_ms, "cspace_call_s": t_cspace},
         "result": {"clusters": int(ncl), "used_beams": used_beams, "n_after_resample": int(side.cur.sample_count),
+                   "cumsum_fallbacks": int(lib.amclb200_cumsum_fallbacks()),
                    "leaf_count": int(side.cur.kdtree.contents.leaf_count)},
     }
     if not args.no_cpu_baseline:

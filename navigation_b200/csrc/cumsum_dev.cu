@@ -201,6 +201,7 @@ __global__ void cs_classify(const double *__restrict__ tile_sum, const double *_
   // leaves weights 300 orders of magnitude apart) are still classified exactly.
   const double eps = 4.0 * (double)n * 1.1102230246251565e-16;
   double run = s_part[threadIdx.x];
+  int my_dirty = 0;
   for (int t = lo; t < hi; t++)
   {
     const double before = run;
@@ -221,15 +222,36 @@ __global__ void cs_classify(const double *__restrict__ tile_sum, const double *_
       if (e0 == e1 && e0 > -1020 && e0 < 1020) cls = e0;
     }
     tile_class[t] = cls;
-    if (cls == kDirty)
+    if (cls == kDirty) my_dirty++;
+  }
+  // Rows of the dirty tiles in TILE ORDER: every rank of a sharded filter runs this
+  // kernel on the same sums and must give the same tile the same row.
+  __shared__ int s_cnt[1024];
+  __syncthreads();
+  s_cnt[threadIdx.x] = my_dirty;
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+    int acc = 0;
+    for (int k = 0; k < (int)blockDim.x; k++)
     {
-      const int row = atomicAdd(dirty_count, 1);
-      if (dirty_row)
+      const int v = s_cnt[k];
+      s_cnt[k] = acc;
+      acc += v;
+    }
+    *dirty_count = acc;
+    if (overflow && acc > max_rows) *overflow = 1;
+  }
+  __syncthreads();
+  if (dirty_row)
+  {
+    int row = s_cnt[threadIdx.x];
+    for (int t = lo; t < hi; t++)
+      if (tile_class[t] == kDirty)
       {
         dirty_row[t] = row < max_rows ? row : -1;
-        if (row >= max_rows) *overflow = 1;
+        row++;
       }
-    }
   }
 }
 

@@ -78,6 +78,7 @@ def main():
                 coll.attach(lib, side.pf, peer_access=p2p)          # torch.distributed callbacks
         side.set_samples(cloud)            # replicated start on every rank
         log = []
+        fallbacks0 = lib.amclb200_cumsum_fallbacks()
         for step in range(3):
             side.update_action((0.1 * step, 0.0, 0.02), (0.1, 0.0, 0.02))
             if model == "lfp_skip":
@@ -98,6 +99,9 @@ def main():
                             ncl=side.cur.cluster_count, conv=side.pf.contents.converged, neff=neff,
                             src=src[lo:hi].copy(), lo=lo, hi=hi, samples=samples,
                             mean=np.array(side.cur.mean.tolist()), table=side.cluster_table()))
+        # the exact table -- each rank's own slice of it when sharded -- must hold its
+        # own recurrence check: a fallback to the replicated walk is correct but is a bug
+        assert lib.amclb200_cumsum_fallbacks() == fallbacks0, "cumulative table fell back (%s)" % mode
         results[mode] = log
         side.close()
 
