@@ -136,7 +136,8 @@ __device__ PairFn block_scan_fn(PairFn v, PairFn *total, PairFn *s_warp)
 // writes them out contiguously: the four later passes then read 8 B per weight
 // instead of dragging the whole record through the memory system each time.
 __global__ void cs_tile_sums(const Weights W, int n, double *__restrict__ tile_sum,
-                             double *__restrict__ tile_max, double *__restrict__ packed, int tile0)
+                             double *__restrict__ tile_max, double *__restrict__ packed, int tile0,
+                             int ts /* element stride of tile_sum / tile_max: 2 when they interleave */)
 {
   __shared__ double s_red[32];
   const int tile = (int)blockIdx.x + tile0;
@@ -163,8 +164,8 @@ __global__ void cs_tile_sums(const Weights W, int n, double *__restrict__ tile_s
   if (threadIdx.x == 0)
   {
     for (int k = 1; k < (int)(blockDim.x >> 5); k++) mx = fmax(mx, s_red[k]);
-    tile_sum[tile] = t;
-    tile_max[tile] = mx;
+    tile_sum[(size_t)tile * ts] = t;
+    tile_max[(size_t)tile * ts] = mx;
   }
 }
 
@@ -173,14 +174,14 @@ __global__ void cs_tile_sums(const Weights W, int n, double *__restrict__ tile_s
 // the dirty tiles publish their weights; a count beyond max_rows raises *overflow.
 __global__ void cs_classify(const double *__restrict__ tile_sum, const double *__restrict__ tile_max,
                             int tiles, int n, int *__restrict__ tile_class, int *dirty_count,
-                            int *__restrict__ dirty_row, int max_rows, int *overflow)
+                            int *__restrict__ dirty_row, int max_rows, int *overflow, int ts)
 {
   __shared__ double s_part[1024];
   // pass 1: grand total (each thread a contiguous slab, then a serial combine)
   const int per = (tiles + blockDim.x - 1) / blockDim.x;
   const int lo = threadIdx.x * per, hi = min(tiles, lo + per);
   double acc = 0.0;
-  for (int t = lo; t < hi; t++) acc += tile_sum[t];
+  for (int t = lo; t < hi; t++) acc += tile_sum[(size_t)t * ts];
   s_part[threadIdx.x] = acc;
   __syncthreads();
   if (threadIdx.x == 0)
@@ -206,7 +207,7 @@ __global__ void cs_classify(const double *__restrict__ tile_sum, const double *_
   {
     const double before = run;
     const double start = run * (1.0 - eps);
-    run += tile_sum[t];
+    run += tile_sum[(size_t)t * ts];
     const double end = run * (1.0 + eps);
     int cls = kDirty;
     (void)before;
@@ -214,7 +215,8 @@ __global__ void cs_classify(const double *__restrict__ tile_sum, const double *_
     // is 0, and also when the largest weight is below a quarter ulp of the
     // smallest value the running sum can have here (c + w rounds back to c,
     // whatever the binade -- the tail of a likelihood_field_prob posterior).
-    if (tile_sum[t] == 0.0 || (start > 0.0 && tile_max[t] < start * 2.7755575615628914e-17))
+    if (tile_sum[(size_t)t * ts] == 0.0 ||
+        (start > 0.0 && tile_max[(size_t)t * ts] < start * 2.7755575615628914e-17))
       cls = kFlat;
     else if (start > 0.0 && isfinite(end))
     {
@@ -758,7 +760,7 @@ static void ensure_tile_scratch(PfCtx *c, int tiles)
   if (tiles <= c->tile_cap) return;
   if (c->d_tile_sum) { cudaFree(c->d_tile_sum); cudaFree(c->d_tile_carry); cudaFree(c->d_tile_fn); cudaFree(c->d_tile_class); }
   c->tile_cap = tiles + 64;
-  AMCL_CUDA(cudaMalloc(&c->d_tile_sum, sizeof(double) * (size_t)c->tile_cap));
+  AMCL_CUDA(cudaMalloc(&c->d_tile_sum, sizeof(double) * 2 * (size_t)c->tile_cap));   // room for (sum, max) pairs
   AMCL_CUDA(cudaMalloc(&c->d_tile_carry, sizeof(double) * (size_t)c->tile_cap));
   AMCL_CUDA(cudaMalloc(&c->d_tile_fn, sizeof(PairFn) * (size_t)c->tile_cap));
   AMCL_CUDA(cudaMalloc(&c->d_tile_class, sizeof(int) * (size_t)c->tile_cap));
@@ -806,23 +808,22 @@ bool exact_cumsum_sharded(PfCtx *c, const Particle *set, int n, double *d_cum)
   Trace tr;
   tr.mark("start");
   // tiles beyond this rank's (and beyond the table's end) must not carry stale sums
-  AMCL_CUDA(cudaMemsetAsync(c->d_tile_sum + tile0, 0, sizeof(double) * (size_t)chunk_tiles, st));
-  AMCL_CUDA(cudaMemsetAsync(c->d_tile_carry + tile0, 0, sizeof(double) * (size_t)chunk_tiles, st));
+  // (sum, maximum) of a tile side by side: one all-gather moves both
+  AMCL_CUDA(cudaMemsetAsync(c->d_tile_sum + 2 * (size_t)tile0, 0, sizeof(double) * 2 * (size_t)chunk_tiles, st));
   if (own > 0)
   {
-    cs_tile_sums<<<own, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_carry, c->d_wpack, tile0);
+    cs_tile_sums<<<own, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_sum + 1, c->d_wpack, tile0, 2);
     AMCL_LAUNCH_CHECK();
   }
   W.p = c->d_wpack;
   W.stride = 1;
-  sh.allgather(c->d_tile_sum, (unsigned long long)chunk_tiles * sizeof(double));
-  sh.allgather(c->d_tile_carry, (unsigned long long)chunk_tiles * sizeof(double));   // the tile maxima
-  tr.mark("sums+2ag");
+  sh.allgather(c->d_tile_sum, (unsigned long long)chunk_tiles * 2 * sizeof(double));
+  tr.mark("sums+ag");
   const int bad_slot = 8, dirty_slot = 9, overflow_slot = 10;
   AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, 3 * sizeof(int), st));
-  cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, c->d_tile_carry, tiles, n, c->d_tile_class,
+  cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, c->d_tile_sum + 1, tiles, n, c->d_tile_class,
                                  c->d_ints + dirty_slot, c->d_dirty_row, kMaxDirtyRows,
-                                 c->d_ints + overflow_slot);
+                                 c->d_ints + overflow_slot, 2);
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaMemsetAsync(c->d_dirty_w, 0, sizeof(double) * (size_t)kMaxDirtyRows * kTileLen, st));
   if (own > 0)
@@ -885,7 +886,7 @@ void exact_cumsum_parallel(PfCtx *c, Weights W, int n, double *d_cum)
     if (!c->d_wpack) AMCL_CUDA(cudaMalloc(&c->d_wpack, sizeof(double) * (size_t)c->alloc_samples));
     packed = c->d_wpack;
   }
-  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_carry, packed, 0);
+  cs_tile_sums<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_sum, c->d_tile_carry, packed, 0, 1);
   AMCL_LAUNCH_CHECK();
   if (packed)
   {
@@ -895,7 +896,7 @@ void exact_cumsum_parallel(PfCtx *c, Weights W, int n, double *d_cum)
   const int bad_slot = 8, dirty_slot = 9;
   AMCL_CUDA(cudaMemsetAsync(c->d_ints + bad_slot, 0, 2 * sizeof(int), st));
   cs_classify<<<1, 1024, 0, st>>>(c->d_tile_sum, c->d_tile_carry, tiles, n, c->d_tile_class,
-                                 c->d_ints + dirty_slot, nullptr, 0, nullptr);
+                                 c->d_ints + dirty_slot, nullptr, 0, nullptr, 1);
   AMCL_LAUNCH_CHECK();
   cs_tile_fns<<<tiles, kTileThreads, 0, st>>>(W, n, c->d_tile_class, tile_fn, 0);
   AMCL_LAUNCH_CHECK();
