@@ -319,92 +319,15 @@ __device__ __forceinline__ int table_rank(const double *__restrict__ coarse, int
 // b = 0..buckets (buckets is a power of two, so b / buckets and r * buckets are
 // exact).  A draw r in [b/buckets, (b+1)/buckets) then has its answer inside
 // [index[b], index[b+1]] -- a handful of neighbouring entries instead of a
-// 24-level search through 128 MB.
-// It is built for MANY buckets (about four table entries each, so that a draw's
-// search stays inside one 32-byte sector of the table) without a search per bucket:
-// index[b] is a step function of b that rises to j
-// at b = ceil(cum[j] * buckets).  One pass over the table writes j at those heads
-// (cum * buckets and the ceiling are exact), an inclusive MAX scan fills the steps.
-__global__ void bucket_heads(const double *__restrict__ cum, int n, int buckets, unsigned int *__restrict__ index)
+// 24-level search through 128 MB.  Built with one full search per bucket,
+// 1/16 of the searches the draws themselves would need.
+__global__ void build_bucket_index(const double *__restrict__ coarse, int n_coarse,
+                                   const double *__restrict__ cum, int n, int buckets,
+                                   int *__restrict__ index)
 {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x + 1;      // table entries 1..n
-  if (j > n) return;
-  const double c = cum[j];
-  if (!(c >= 0.0) || c * (double)buckets > (double)buckets) return;   // beyond the last bucket (or NaN)
-  const int lo = (int)ceil(c * (double)buckets);
-  // equal entries share a head: the largest j must win
-  atomicMax(&index[lo], (unsigned int)j);
-}
-
-__global__ void maxscan_tile_max(const unsigned int *__restrict__ in, int n, unsigned int *__restrict__ tile_max)
-{
-  __shared__ unsigned int s_red[32];
-  const int base = blockIdx.x * kScanTile;
-  unsigned int v = 0;
-  for (int k = 0; k < kScanItems; k++)
-  {
-    const int i = base + k * kScanThreads + threadIdx.x;
-    if (i < n) v = max(v, in[i]);
-  }
-  v = __reduce_max_sync(kFullMask, v);
-  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
-  __syncthreads();
-  if (threadIdx.x == 0)
-  {
-    for (int k = 1; k < (int)(blockDim.x >> 5); k++) v = max(v, s_red[k]);
-    tile_max[blockIdx.x] = v;
-  }
-}
-
-// single block: exclusive max-scan of the tile maxima in place
-__global__ void maxscan_tile_offsets(unsigned int *tile_max, int tiles)
-{
-  if (threadIdx.x != 0) return;
-  unsigned int run = 0;
-  for (int t = 0; t < tiles; t++)
-  {
-    const unsigned int v = tile_max[t];
-    tile_max[t] = run;
-    run = max(run, v);
-  }
-}
-
-__global__ void maxscan_apply(unsigned int *__restrict__ data, int n, const unsigned int *__restrict__ tile_offsets)
-{
-  __shared__ unsigned int s_warp[kScanThreads / 32];
-  const int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
-  unsigned int item[kScanItems];
-  unsigned int v = 0;
-#pragma unroll
-  for (int k = 0; k < kScanItems; k++)
-  {
-    const int i = base + k;
-    item[k] = i < n ? data[i] : 0u;
-    v = max(v, item[k]);
-  }
-  // inclusive max over the threads of the block, in thread order
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  unsigned int inc = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1)
-  {
-    const unsigned int up = __shfl_up_sync(kFullMask, inc, o);
-    if (lane >= o) inc = max(inc, up);
-  }
-  if (lane == 31) s_warp[wid] = inc;
-  __syncthreads();
-  unsigned int before = tile_offsets[blockIdx.x];
-  for (int w = 0; w < wid; w++) before = max(before, s_warp[w]);
-  unsigned int ex = __shfl_up_sync(kFullMask, inc, 1);
-  if (lane == 0) ex = 0u;
-  unsigned int run = max(before, ex);
-#pragma unroll
-  for (int k = 0; k < kScanItems; k++)
-  {
-    run = max(run, item[k]);
-    const int i = base + k;
-    if (i < n) data[i] = run;
-  }
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > buckets) return;
+  index[b] = table_rank(coarse, n_coarse, cum, n, (double)b / (double)buckets);
 }
 
 struct PickArgs
@@ -2089,7 +2012,7 @@ void run_resample(PfCtx *c)
   pa.cum = c->d_cum;
   pa.coarse = nullptr;
   pa.n_coarse = n_a / kCoarse;
-  if (pa.n_coarse >= 64 && n_a < (1 << 16))     // larger tables are searched through the bucket index
+  if (pa.n_coarse >= 64)
   {
     // the draws array has room behind the 2*maxs uniforms? no: use the partial-sum scratch
     ensure_partials(c, pa.n_coarse);
@@ -2102,24 +2025,15 @@ void run_resample(PfCtx *c)
   if (n_a >= (1 << 16))
   {
     int buckets = 1;
-    while (buckets * 4 < n_a) buckets <<= 1;      // about 4 table entries (one 32-byte sector) per bucket
-    const int tiles = (buckets + 1 + kScanTile - 1) / kScanTile;
-    if ((size_t)buckets + 1 + (size_t)tiles > c->bucket_cap)
+    while (buckets * 16 < n_a) buckets <<= 1;     // about 16 table entries per bucket
+    if ((size_t)buckets + 1 > c->bucket_cap)
     {
       if (c->d_bucket_index) cudaFree(c->d_bucket_index);
-      c->bucket_cap = (size_t)buckets + 1 + (size_t)tiles;
+      c->bucket_cap = (size_t)buckets + 1;
       AMCL_CUDA(cudaMalloc(&c->d_bucket_index, sizeof(int) * c->bucket_cap));
     }
-    unsigned int *index = reinterpret_cast<unsigned int *>(c->d_bucket_index);
-    unsigned int *tile_max = index + buckets + 1;
-    AMCL_CUDA(cudaMemsetAsync(index, 0, sizeof(unsigned int) * (size_t)(buckets + 1), st));
-    bucket_heads<<<blocks_for(n_a, 256), 256, 0, st>>>(c->d_cum, n_a, buckets, index);
-    AMCL_LAUNCH_CHECK();
-    maxscan_tile_max<<<tiles, kScanThreads, 0, st>>>(index, buckets + 1, tile_max);
-    AMCL_LAUNCH_CHECK();
-    maxscan_tile_offsets<<<1, 32, 0, st>>>(tile_max, tiles);
-    AMCL_LAUNCH_CHECK();
-    maxscan_apply<<<tiles, kScanThreads, 0, st>>>(index, buckets + 1, tile_max);
+    build_bucket_index<<<blocks_for(buckets + 1, 256), 256, 0, st>>>(pa.coarse, pa.n_coarse, c->d_cum, n_a,
+                                                                     buckets, c->d_bucket_index);
     AMCL_LAUNCH_CHECK();
     pa.bucket_index = c->d_bucket_index;
     pa.buckets = buckets;
