@@ -77,12 +77,16 @@ __global__ void ingest_image_kernel(const IngestArgs a)
 // tf2::Quaternion::setRPY(0, 0, yaw) (geometry2 tf2/LinearMath/Quaternion.h,
 // not vendored in the reference tree) written out term by term so that the
 // signs of the zero components come out as tf2's do.
+// own_lo / own_hi: the samples this rank holds (a sharded filter packs only those; the
+// entries of the others stay zero and a SUM all-reduce completes the cloud).
 __global__ void pack_cloud_kernel(const Particle *__restrict__ set, int n, int stride, int count,
-                                  double *__restrict__ out)
+                                  double *__restrict__ out, int own_lo, int own_hi)
 {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= count) return;
-  const Particle s = load_particle(set + (size_t)k * stride);
+  const long long idx = (long long)k * stride;
+  if (idx < own_lo || idx >= own_hi) return;
+  const Particle s = load_particle(set + (size_t)idx);
   const double half_yaw = s.th * 0.5, half_pitch = 0.0 * 0.5, half_roll = 0.0 * 0.5;
   double sy, cy;
   sincos(half_yaw, &sy, &cy);
@@ -186,7 +190,10 @@ int amclb200_pf_pack_cloud(pf_t *pf, int stride, int max_poses, double *out)
   int count = (n + stride - 1) / stride;
   if (count > max_poses) count = max_poses;
   if (count <= 0 || !out) return 0;
-  pf_replicate(c, which);   // sharded filters: every rank packs the same cloud
+  // A sharded filter does not gather the whole set for a decimated cloud: every rank
+  // packs the poses it holds, the rest of its buffer is zero, one SUM all-reduce of
+  // the packed cloud (56 B per pose) gives everybody all of it.
+  const bool sliced = c->shard.on() && !c->replicated[which];
   cudaStream_t st = globals().stream;
   const size_t bytes = sizeof(double) * 7 * (size_t)count;
   if (bytes > c->cloud_cap)
@@ -195,8 +202,16 @@ int amclb200_pf_pack_cloud(pf_t *pf, int stride, int max_poses, double *out)
     c->cloud_cap = bytes + 7 * sizeof(double) * 1024;
     AMCL_CUDA(cudaMalloc(&c->d_cloud, c->cloud_cap));
   }
-  pack_cloud_kernel<<<(count + 255) / 256, 256, 0, st>>>(c->d_set[which], n, stride, count, c->d_cloud);
+  if (sliced) AMCL_CUDA(cudaMemsetAsync(c->d_cloud, 0, bytes, st));
+  pack_cloud_kernel<<<(count + 255) / 256, 256, 0, st>>>(c->d_set[which], n, stride, count, c->d_cloud,
+                                                         sliced ? c->shard.lo(n) : 0, sliced ? c->shard.hi(n) : n);
   AMCL_LAUNCH_CHECK();
+  if (sliced)
+    for (size_t off = 0; off < 7 * (size_t)count; off += (size_t)1 << 28)
+    {
+      const size_t len = 7 * (size_t)count - off < ((size_t)1 << 28) ? 7 * (size_t)count - off : (size_t)1 << 28;
+      c->shard.allreduce(c->d_cloud + off, (int)len, SHARD_F64, SHARD_SUM);
+    }
   AMCL_CUDA(cudaMemcpyAsync(out, c->d_cloud, bytes, cudaMemcpyDeviceToHost, st));
   AMCL_CUDA(cudaStreamSynchronize(st));
   return count;

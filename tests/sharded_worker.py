@@ -94,10 +94,15 @@ def main():
             src = np.empty(n, np.int32)
             cnt = lib.amclb200_pf_resample_sources(side.pf, src.ctypes.data, n)
             lo, hi = (0, cnt) if mode == "single" else sharded.shard_range(cnt, rank, world)
+            # the decimated PoseArray, packed BEFORE anything replicates the set: every
+            # rank packs its own poses and one small all-reduce completes the cloud
+            packed = np.zeros((64, 7))
+            got = lib.amclb200_pf_pack_cloud(side.pf, max(1, cnt // 50), 64, packed.ctypes.data)
+            packed = packed[:got].copy()
             samples = side.samples()       # pulls (all-gathers first when sharded)
             log.append(dict(n=side.cur.sample_count, k=side.cur.kdtree.contents.leaf_count,
                             ncl=side.cur.cluster_count, conv=side.pf.contents.converged, neff=neff,
-                            src=src[lo:hi].copy(), lo=lo, hi=hi, samples=samples,
+                            src=src[lo:hi].copy(), lo=lo, hi=hi, samples=samples, packed=packed,
                             mean=np.array(side.cur.mean.tolist()), table=side.cluster_table()))
         # the exact table -- each rank's own slice of it when sharded -- must hold its
         # own recurrence check: a fallback to the replicated walk is correct but is a bug
@@ -114,6 +119,7 @@ def main():
         assert np.array_equal(a["samples"][:, :3], b["samples"][:, :3])
         assert np.allclose(a["samples"][:, 3], b["samples"][:, 3], rtol=1e-12, atol=0)
         assert np.allclose(a["mean"], b["mean"], rtol=1e-9, atol=1e-12)
+        assert a["packed"].shape[0] > 0 and np.array_equal(a["packed"], b["packed"])
         wa = sorted(t[0] for t in a["table"])
         wb = sorted(t[0] for t in b["table"])
         assert np.allclose(wa, wb, rtol=1e-9, atol=1e-15)
