@@ -68,7 +68,9 @@ struct MapCtx
   uint16_t *d_code = nullptr;     // tiled distance codes
   uint64_t *d_blocked = nullptr;  // 8x8-cell bit tiles: bit set = ray stops here
   int btiles_x = 0, btiles_y = 0;
-  uint8_t *d_rowdist = nullptr;   // EDT scratch: distance along the row, one byte per cell
+  uint8_t *d_rowdist = nullptr;   // EDT scratch (search kernels): distance along the row, one byte per cell
+  uint16_t *d_rowsq = nullptr;    // EDT scratch: its square, rows of (sx rounded up to 8) cells
+  size_t rowsq_cap = 0;
   unsigned long long *d_rowbits = nullptr;  // EDT scratch: occupancy bit strings per row
   size_t rowbits_cap = 0;
   float ms_edt = 0;               // device time of the last distance transform (3 kernels)

@@ -25,6 +25,7 @@
 
 #include "context.hpp"
 #include "edt_rows.cuh"
+#include "edt_squares.cuh"
 
 namespace amclb200
 {
@@ -165,7 +166,6 @@ MapCtx *map_ctx(map_t *map, bool create)
   AMCL_CUDA(cudaMalloc(&m->d_occ, cells));
   AMCL_CUDA(cudaMalloc(&m->d_code, (size_t)m->tiles_x * m->tiles_y * 16 * sizeof(uint16_t)));
   AMCL_CUDA(cudaMalloc(&m->d_blocked, (size_t)m->btiles_x * m->btiles_y * sizeof(uint64_t)));
-  AMCL_CUDA(cudaMalloc(&m->d_rowdist, cells));
   r[map] = m;
   return m;
 }
@@ -179,7 +179,8 @@ void map_ctx_release(map_t *map)
   cudaFree(m->d_occ);
   cudaFree(m->d_code);
   cudaFree(m->d_blocked);
-  cudaFree(m->d_rowdist);
+  if (m->d_rowdist) cudaFree(m->d_rowdist);
+  if (m->d_rowsq) cudaFree(m->d_rowsq);
   if (m->d_rowbits) cudaFree(m->d_rowbits);
   if (m->d_lf) cudaFree(m->d_lf);
   if (m->d_rank_of_code) cudaFree(m->d_rank_of_code);
@@ -539,37 +540,76 @@ void map_build_distance_codes(MapCtx *m, double max_occ_dist)
   set_code_table(m, max_occ_dist);
   cudaStream_t st = globals().stream;
   const int R = m->R;
-  const int words = (m->sx + 63) / 64;
-  const int pad = (R + 1 + 63) / 64 + 1;
-  const size_t nbits = (size_t)m->sy * (words + 2 * pad);
+  const EdtPlan plan = edt_plan(m->sx, m->sy, R);
+  const int words = plan.words, pad = plan.pad;
+  const size_t nbits = (size_t)m->sy * plan.stride;
   if (nbits > m->rowbits_cap)
   {
     if (m->d_rowbits) cudaFree(m->d_rowbits);
     m->rowbits_cap = nbits;
     AMCL_CUDA(cudaMalloc(&m->d_rowbits, nbits * sizeof(unsigned long long)));
   }
+  if (m->sy > 65535) AMCL_FATAL("maps taller than 65535 rows are not supported (%d)", m->sy);
+  // AMCLB200_EDT=search keeps the per-cell search kernels for any radius (A/B timing)
+  static const bool force_search = [] {
+    const char *e = getenv("AMCLB200_EDT");
+    return e && strcmp(e, "search") == 0;
+  }();
+  const bool fast = R <= kFastRadius && !force_search;
+  const int pitch = plan.pitch;
+  if (fast && (size_t)pitch * m->sy > m->rowsq_cap)
+  {
+    if (m->d_rowsq) cudaFree(m->d_rowsq);
+    m->rowsq_cap = (size_t)pitch * m->sy;
+    AMCL_CUDA(cudaMalloc(&m->d_rowsq, m->rowsq_cap * sizeof(uint16_t)));
+  }
+  if (!fast && !m->d_rowdist) AMCL_CUDA(cudaMalloc(&m->d_rowdist, (size_t)m->sx * m->sy));
   cudaEvent_t ev0, ev1;
   AMCL_CUDA(cudaEventCreate(&ev0));
   AMCL_CUDA(cudaEventCreate(&ev1));
   AMCL_CUDA(cudaEventRecord(ev0, st));
+  if (fast && (m->sx & 15) == 0)
+  {
+    edt_pack_rows16<<<(unsigned)((plan.pack_threads + 255) / 256), 256, 0, st>>>(m->d_occ, m->sx, m->sy, words, pad,
+                                                                       m->d_rowbits);
+    AMCL_LAUNCH_CHECK();
+  }
+  else
   {
     const long long warps = (long long)m->sy * (words + 2 * pad);
     edt_pack_rows<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(m->d_occ, m->sx, m->sy, words, pad,
                                                                m->d_rowbits);
     AMCL_LAUNCH_CHECK();
   }
-  if (m->sy > 65535) AMCL_FATAL("maps taller than 65535 rows are not supported (%d)", m->sy);
-  dim3 g1((m->sx + 1023) / 1024, m->sy);     // four cells per thread
-  edt_row_bits<<<g1, 256, 0, st>>>(m->d_rowbits, m->sx, m->sy, words, pad, R, m->d_rowdist);
-  AMCL_LAUNCH_CHECK();
-  dim3 g2((m->sx + 1 + kPatchX - 1) / kPatchX, (m->sy + 1 + kPatchY - 1) / kPatchY);  // + padding
-  size_t smem = (((size_t)(kPatchY + 2 * R) * kPatchX + 15) & ~(size_t)15) +
-                (size_t)kPatchX * kPatchY * sizeof(uint16_t);
-  if (smem > 48 * 1024)
-    AMCL_CUDA(cudaFuncSetAttribute(edt_col_pass, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)smem));
-  edt_col_pass<<<g2, 256, smem, st>>>(m->d_rowdist, m->sx, m->sy, R, m->tiles_x, m->d_code);
-  AMCL_LAUNCH_CHECK();
+  if (fast)
+  {
+    dim3 g1(plan.row_blocks_x, m->sy);          // eight cells per thread
+    edt_row_squares<<<g1, 256, 0, st>>>(m->d_rowbits, pitch, words, pad, R, m->d_rowsq);
+    AMCL_LAUNCH_CHECK();
+    const int chunks = plan.chunks;
+    dim3 g2(plan.col_blocks_x, plan.col_blocks_y);
+    const size_t smem = plan.col_smem;
+    if (smem > 48 * 1024)
+      AMCL_CUDA(cudaFuncSetAttribute(edt_col_squares, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+    edt_col_squares<<<g2, 256, smem, st>>>(m->d_rowsq, pitch, m->sx, m->sy, R, chunks, m->tiles_x,
+                                           m->tiles_y, m->d_code);
+    AMCL_LAUNCH_CHECK();
+  }
+  else
+  {
+    dim3 g1((m->sx + 1023) / 1024, m->sy);     // four cells per thread
+    edt_row_bits<<<g1, 256, 0, st>>>(m->d_rowbits, m->sx, m->sy, words, pad, R, m->d_rowdist);
+    AMCL_LAUNCH_CHECK();
+    dim3 g2((m->sx + 1 + kPatchX - 1) / kPatchX, (m->sy + 1 + kPatchY - 1) / kPatchY);  // + padding
+    size_t smem = (((size_t)(kPatchY + 2 * R) * kPatchX + 15) & ~(size_t)15) +
+                  (size_t)kPatchX * kPatchY * sizeof(uint16_t);
+    if (smem > 48 * 1024)
+      AMCL_CUDA(cudaFuncSetAttribute(edt_col_pass, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+    edt_col_pass<<<g2, 256, smem, st>>>(m->d_rowdist, m->sx, m->sy, R, m->tiles_x, m->d_code);
+    AMCL_LAUNCH_CHECK();
+  }
   AMCL_CUDA(cudaEventRecord(ev1, st));
   AMCL_CUDA(cudaEventSynchronize(ev1));
   AMCL_CUDA(cudaEventElapsedTime(&m->ms_edt, ev0, ev1));

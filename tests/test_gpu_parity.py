@@ -44,7 +44,9 @@ def lib(gpu_lib):
 
 # ------------------------------------------------------------------ a9: EDT ----
 
-@pytest.mark.parametrize("size,max_d,scale", [(160, 1.0, 0.05), (333, 2.0, 0.05), (97, 0.3, 0.1)])
+@pytest.mark.parametrize("size,max_d,scale", [(160, 1.0, 0.05), (333, 2.0, 0.05), (97, 0.3, 0.1),
+                                              (208, 2.0, 0.05),      # rows of 16-byte multiples: edt_pack_rows16
+                                              (208, 9.0, 0.05)])     # 180 cells > kFastRadius: the search kernels
 def test_edt_bit_exact_vs_oracle(lib, port, size, max_d, scale):
     occ = synth.rooms_map(size, seed=size, room=50, door=(20, 30), clutter_mod=300,
                           unknown_ring=True)
