@@ -71,6 +71,9 @@ struct MapCtx
   uint8_t *d_rowdist = nullptr;   // EDT scratch (search kernels): distance along the row, one byte per cell
   uint16_t *d_rowsq = nullptr;    // EDT scratch: its square, rows of (sx rounded up to 8) cells
   size_t rowsq_cap = 0;
+  int8_t *h_occ_pin = nullptr;    // page-locked staging of the occupancy states / the codes
+  uint16_t *h_code_pin = nullptr; // (eager mirror: map_update_cspace through the unchanged API)
+  size_t h_occ_cap = 0, h_code_cap = 0;
   unsigned long long *d_rowbits = nullptr;  // EDT scratch: occupancy bit strings per row
   size_t rowbits_cap = 0;
   float ms_edt = 0;               // device time of the last distance transform (3 kernels)

@@ -181,6 +181,8 @@ void map_ctx_release(map_t *map)
   cudaFree(m->d_blocked);
   if (m->d_rowdist) cudaFree(m->d_rowdist);
   if (m->d_rowsq) cudaFree(m->d_rowsq);
+  if (m->h_occ_pin) cudaFreeHost(m->h_occ_pin);
+  if (m->h_code_pin) cudaFreeHost(m->h_code_pin);
   if (m->d_rowbits) cudaFree(m->d_rowbits);
   if (m->d_lf) cudaFree(m->d_lf);
   if (m->d_rank_of_code) cudaFree(m->d_rank_of_code);
@@ -377,31 +379,57 @@ void parallel_rows(int rows, const std::function<void(int, int)> &body)
 }
 
 
+// Page-locked staging that lives as long as the map: a pageable std::vector per
+// call costs a page fault per 4 KB and a bounce copy inside the driver.
+template <typename T>
+static T *pinned_staging(T **slot, size_t *cap, size_t count)
+{
+  if (count > *cap)
+  {
+    if (*slot) cudaFreeHost(*slot);
+    *slot = nullptr;
+    AMCL_CUDA(cudaHostAlloc((void **)slot, count * sizeof(T), cudaHostAllocDefault));
+    *cap = count;
+  }
+  return *slot;
+}
+
+// Bands of rows the host <-> device conversions are pipelined in: the copy of
+// one band runs while the host cores convert the next.
+static int staging_bands(size_t cells) { return cells >= ((size_t)1 << 20) ? 4 : 1; }
+
 void map_upload_occupancy(MapCtx *m)
 {
   const map_t *map = m->host;
   size_t cells = (size_t)m->sx * m->sy;
-  std::vector<int8_t> occ(cells);
+  int8_t *occ = pinned_staging(&m->h_occ_pin, &m->h_occ_cap, cells);
   const int sx = m->sx;
-  parallel_rows(m->sy, [&](int j0, int j1) {
-    for (int j = j0; j < j1; j++)
-    {
-      const map_cell_t *row = map->cells + (size_t)j * sx;
-      int8_t *o = occ.data() + (size_t)j * sx;
-      for (int i = 0; i < sx; i++)
-      {
-        const int st = row[i].occ_state;
-        o[i] = (int8_t)(st > 0 ? 1 : (st < 0 ? -1 : 0));
-      }
-    }
-  });
   cudaStream_t st = globals().stream;
-  AMCL_CUDA(cudaMemcpyAsync(m->d_occ, occ.data(), cells, cudaMemcpyHostToDevice, st));
+  const int bands = staging_bands(cells);
+  for (int b = 0; b < bands; b++)
+  {
+    const int r0 = (int)((long long)m->sy * b / bands), r1 = (int)((long long)m->sy * (b + 1) / bands);
+    if (r1 <= r0) continue;
+    parallel_rows(r1 - r0, [&](int j0, int j1) {
+      for (int j = r0 + j0; j < r0 + j1; j++)
+      {
+        const map_cell_t *row = map->cells + (size_t)j * sx;
+        int8_t *o = occ + (size_t)j * sx;
+        for (int i = 0; i < sx; i++)
+        {
+          const int state = row[i].occ_state;
+          o[i] = (int8_t)(state > 0 ? 1 : (state < 0 ? -1 : 0));
+        }
+      }
+    });
+    AMCL_CUDA(cudaMemcpyAsync(m->d_occ + (size_t)r0 * sx, occ + (size_t)r0 * sx, (size_t)(r1 - r0) * sx,
+                              cudaMemcpyHostToDevice, st));
+  }
   int nt = m->btiles_x * m->btiles_y;
   build_blocked_bits<<<(nt + 255) / 256, 256, 0, st>>>(m->d_occ, m->sx, m->sy, m->btiles_x,
                                                          m->btiles_y, m->d_blocked);
   AMCL_LAUNCH_CHECK();
-  AMCL_CUDA(cudaStreamSynchronize(st));  // occ is a stack-lifetime staging buffer
+  AMCL_CUDA(cudaStreamSynchronize(st));  // the staging buffer is free for the next call
   m->occ_uploaded = true;
 }
 
@@ -622,21 +650,41 @@ void map_build_distance_codes(MapCtx *m, double max_occ_dist)
 void map_codes_to_host_cells(MapCtx *m)
 {
   size_t ncodes = (size_t)m->tiles_x * m->tiles_y * 16;
-  std::vector<uint16_t> codes(ncodes);
-  AMCL_CUDA(cudaMemcpyAsync(codes.data(), m->d_code, ncodes * sizeof(uint16_t),
-                            cudaMemcpyDeviceToHost, globals().stream));
-  AMCL_CUDA(cudaStreamSynchronize(globals().stream));
+  uint16_t *codes = pinned_staging(&m->h_code_pin, &m->h_code_cap, ncodes);
+  cudaStream_t st = globals().stream;
+  // bands of tile rows (a tile row is contiguous): band b + 1 crosses PCIe while the
+  // host cores spread band b over the caller's 16-byte cells
+  const int bands = staging_bands((size_t)m->sx * m->sy);
+  cudaEvent_t arrived[4];
+  int t_lo[4], t_hi[4];
+  for (int b = 0; b < bands; b++)
+  {
+    t_lo[b] = (int)((long long)m->tiles_y * b / bands);
+    t_hi[b] = (int)((long long)m->tiles_y * (b + 1) / bands);
+    AMCL_CUDA(cudaEventCreateWithFlags(&arrived[b], cudaEventDisableTiming));
+    const size_t off = (size_t)t_lo[b] * m->tiles_x * 16, len = (size_t)(t_hi[b] - t_lo[b]) * m->tiles_x * 16;
+    if (len)
+      AMCL_CUDA(cudaMemcpyAsync(codes + off, m->d_code + off, len * sizeof(uint16_t), cudaMemcpyDeviceToHost, st));
+    AMCL_CUDA(cudaEventRecord(arrived[b], st));
+  }
   map_t *map = m->host;
   const double *lut = m->dist_of_code.data();
-  parallel_rows(m->sy, [&](int j0, int j1) {
-    for (int j = j0; j < j1; j++)
-    {
-      const uint16_t *trow = codes.data() + (size_t)(j >> 2) * m->tiles_x * 16 + (j & 3) * 4;
-      map_cell_t *crow = map->cells + (size_t)j * m->sx;
-      for (int i = 0; i < m->sx; i++)
-        crow[i].occ_dist = lut[trow[(size_t)(i >> 2) * 16 + (i & 3)]];
-    }
-  });
+  for (int b = 0; b < bands; b++)
+  {
+    AMCL_CUDA(cudaEventSynchronize(arrived[b]));
+    cudaEventDestroy(arrived[b]);
+    const int r0 = t_lo[b] * kTile, r1 = t_hi[b] * kTile < m->sy ? t_hi[b] * kTile : m->sy;
+    if (r1 <= r0) continue;
+    parallel_rows(r1 - r0, [&](int j0, int j1) {
+      for (int j = r0 + j0; j < r0 + j1; j++)
+      {
+        const uint16_t *trow = codes + (size_t)(j >> 2) * m->tiles_x * 16 + (j & 3) * 4;
+        map_cell_t *crow = map->cells + (size_t)j * m->sx;
+        for (int i = 0; i < m->sx; i++)
+          crow[i].occ_dist = lut[trow[(size_t)(i >> 2) * 16 + (i & 3)]];
+      }
+    });
+  }
   map->max_occ_dist = m->max_occ_dist;
 }
 
