@@ -287,10 +287,19 @@ def rooflines(lib, args, k_ms, n_local, used_beams, ms_step, st_action, st_resam
     have_peaks = os.path.exists(peaks_file)
     hbm = json.load(open(peaks_file))["hbm_gbs"] if have_peaks else 6650.0
     hbm_src = "MEASURED_PEAKS.json" if have_peaks else "fallback (B200_PROFILING.md)"
-    rec = None
+    rec, scaled_from = None, None
     cfile = os.path.join(ROOT, "profiles", "lf_counters.json")
     if os.path.exists(cfile) and args.beams == N_BEAMS and args.map_size == MAP_SIZE:
-        rec = json.load(open(cfile)).get(str(n_local))
+        table = {k: v for k, v in json.load(open(cfile)).items() if k.isdigit()}
+        rec = table.get(str(n_local))
+        if rec is None and table:
+            # a slice of the same cloud (uniform over free space): the sectors and DRAM
+            # bytes per particle are those of the recorded launch, scaled by the particle count
+            scaled_from = max(table, key=int)
+            f = n_local / float(scaled_from)
+            rec = dict(table[scaled_from])
+            rec["l2_sectors_read"] = rec["l2_sectors_read"] * f
+            rec["dram_bytes"] = rec["dram_bytes"] * f
     sectors = rec["l2_sectors_read"] if rec else None
     sector_rate = sectors / (k_ms * 1e-3) if sectors else None
     roofline = {
@@ -309,6 +318,9 @@ def rooflines(lib, args, k_ms, n_local, used_beams, ms_step, st_action, st_resam
         "ncu_recorded": ({k: rec[k] for k in ("commit", "l1tex_sectors", "l1tex_lsu_pipe_pct", "issue_active_pct",
                                              "fp64_pipe_pct", "l2_hit_pct", "kernel_ms_under_ncu") if k in rec}
                          if rec else "no recorded capture for %d particles per launch" % n_local),
+        "ncu_scaled_from": (None if scaled_from is None else
+                            "sectors and DRAM bytes of the %s-particle capture x %d / %s (same cloud, a slice of it)"
+                            % (scaled_from, n_local, scaled_from)),
         "achieved_survey_def": alg_bytes / (k_ms * 1e-3) / 1e9,
         "frac_survey_def": alg_bytes / (k_ms * 1e-3) / 1e9 / (gather_rate * 32.0 / 1e9),
         "note": "achieved = L2 sectors the launch reads (ncu) x 32 B / live kernel time; traffic = its DRAM "
@@ -331,7 +343,7 @@ def rooflines(lib, args, k_ms, n_local, used_beams, ms_step, st_action, st_resam
                   "128 B per particle of this rank's slice (SURVEY.md 8d); CUDA events around pf_update_resample"
                   + ("; tables and labelling still work on global objects" if world > 1 else "")),
         hbm_stage("map_update_cspace (EDT)", 3.0 * args.map_size * args.map_size, edt_ms,
-                  "edt_pack_rows, edt_row_bits, edt_col_pass",
+                  "edt_pack_rows16, edt_row_squares, edt_col_squares",
                   "3 B per cell (SURVEY.md 8d); the three kernels only, host cell conversion excluded"),
     ]
     return roofline, stages
