@@ -60,7 +60,7 @@ inline EdtPlan edt_plan(int sx, int sy, int R)
   return p;
 }
 
-__global__ void edt_pack_rows16(const int8_t *__restrict__ occ, int sx, int sy, int words, int pad,
+static __global__ void edt_pack_rows16(const int8_t *__restrict__ occ, int sx, int sy, int words, int pad,
                                 unsigned long long *__restrict__ bits)
 {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -93,7 +93,7 @@ __global__ void edt_pack_rows16(const int8_t *__restrict__ occ, int sx, int sy, 
                                            ((unsigned long long)(m2 | (m3 << 16)) << 32);
 }
 
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 edt_row_squares(const unsigned long long *__restrict__ bits, int pitch, int words, int pad, int R,
                 uint16_t *__restrict__ g2)
 {
@@ -131,32 +131,35 @@ edt_row_squares(const unsigned long long *__restrict__ bits, int pitch, int word
   *reinterpret_cast<uint4 *>(g2 + (size_t)j * pitch + i) = out;
 }
 
-__global__ void __launch_bounds__(256)
-edt_col_squares(const uint16_t *__restrict__ g2, int pitch, int sx, int sy, int R, int chunks,
-                int tiles_x, int tiles_y, uint16_t *__restrict__ code)
+// The column minimum for the block's 128 x 64 outputs.  Output row j (block row
+// j0 + warp * 8 + v) reads source rows j + src_shift - R .. j + src_shift + R of g2,
+// which holds src_rows rows; rows outside it count as "no obstacle".  Leaves
+// min_dj dj^2 + g^2 of columns i0 + 4 * lane .. + 3 in lo[v] (two columns) and hi[v].
+// Every thread of the block must call it (it holds the block's barrier).
+__device__ __forceinline__ void edt_col_block(const uint16_t *__restrict__ g2, int pitch, int src_rows,
+                                              int src_shift, int R, int chunks, int i0, int j0,
+                                              unsigned char *s_raw, unsigned (&lo)[kColV],
+                                              unsigned (&hi)[kColV])
 {
-  extern __shared__ __align__(16) unsigned char s_raw[];
   // rows j0 - R .. of the patch, 128 cells (256 bytes) each; the rows past the
   // halo that the last chunk of 8 touches hold "no obstacle"
   const int rows = kColY - kColV + chunks * 8;
-  const int i0 = blockIdx.x * kColX, j0 = blockIdx.y * kColY;
   const unsigned far2 = (unsigned)((R + 1) * (R + 1)) * 0x10001u;
   {
     uint4 *s4 = reinterpret_cast<uint4 *>(s_raw);
     for (int k = threadIdx.x; k < rows * (kColX / 8); k += blockDim.x)
     {
       const int lj = k / (kColX / 8), c = (k % (kColX / 8)) * 8;
-      const int j = j0 - R + lj, i = i0 + c;
+      const int r = j0 - R + lj + src_shift, i = i0 + c;
       uint4 v = make_uint4(far2, far2, far2, far2);
-      if (lj < kColY + 2 * R && j >= 0 && j < sy && i < pitch)
-        v = __ldg(reinterpret_cast<const uint4 *>(g2 + (size_t)j * pitch + i));
+      if (lj < kColY + 2 * R && r >= 0 && r < src_rows && i < pitch)
+        v = __ldg(reinterpret_cast<const uint4 *>(g2 + (size_t)r * pitch + i));
       s4[k] = v;
     }
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint2 *col = reinterpret_cast<const uint2 *>(s_raw) + (size_t)warp * kColV * (kColX / 4) + lane;
-  unsigned lo[kColV], hi[kColV];
 #pragma unroll
   for (int v = 0; v < kColV; v++) lo[v] = hi[v] = 0xffffffffu;
   // D[k] = dj^2 (in both halves) for dj = t0 + k - 7 - R: source row t0 + u of
@@ -187,6 +190,17 @@ edt_col_squares(const uint16_t *__restrict__ g2, int pitch, int sx, int sy, int 
       }
     }
   }
+}
+
+static __global__ void __launch_bounds__(256)
+edt_col_squares(const uint16_t *__restrict__ g2, int pitch, int sx, int sy, int R, int chunks,
+                int tiles_x, int tiles_y, uint16_t *__restrict__ code)
+{
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  const int i0 = blockIdx.x * kColX, j0 = blockIdx.y * kColY;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned lo[kColV], hi[kColV];
+  edt_col_block(g2, pitch, sy, 0, R, chunks, i0, j0, s_raw, lo, hi);
   // codes: d2 <= R^2 as they are, R^2 + 1 beyond, R^2 + 2 off the map
   const unsigned R2 = (unsigned)(R * R);
   const unsigned beyond2 = (R2 + 1) * 0x10001u, off2 = (R2 + 2) * 0x10001u;

@@ -23,17 +23,10 @@
 #include "amcl_b200.h"
 #include "context.hpp"
 #include "edt_rows.cuh"
+#include "inflation_kernels.cuh"
 
 namespace amclb200
 {
-
-enum { COST_NO_INFORMATION = 255, COST_LETHAL = 254, COST_INSCRIBED = 253, COST_FREE = 0 };  // cost_values.h:42-45
-
-struct InflBox
-{
-  int e_i0, e_j0, e_i1, e_j1;   // seed window: update window grown by R, clipped (inflation_layer.cpp:206-214)
-  int a_i0, a_j0, a_i1, a_j1;   // cells the update can reach: seed window grown by R again, clipped
-};
 
 // One warp per 64-cell word of a seed row.
 __global__ void infl_pack_rows(const unsigned char *__restrict__ master, int pitch, InflBox b,
@@ -130,8 +123,10 @@ struct InflScratch
 {
   unsigned long long *d_bits = nullptr;
   size_t bits_cap = 0;
-  unsigned char *d_g = nullptr;
+  unsigned char *d_g = nullptr;      // row distances, one byte per cell (search kernels)
   size_t g_cap = 0;
+  uint16_t *d_g2 = nullptr;          // their squares, rows of (width rounded up to 8) cells
+  size_t g2_cap = 0;
   unsigned char *d_lut = nullptr;
   size_t lut_cap = 0;
   unsigned char *d_rows = nullptr;   // staging for host-resident grids
@@ -175,15 +170,7 @@ int amclb200_inflate_costs(unsigned char *costs, int on_device, int size_x, int 
   const int R = (int)Ru;
   ensure_device();
   InflBox b;
-  b.e_i0 = max(0, min_i - R);
-  b.e_j0 = max(0, min_j - R);
-  b.e_i1 = min(size_x, max_i + R);
-  b.e_j1 = min(size_y, max_j + R);
-  if (b.e_i0 >= b.e_i1 || b.e_j0 >= b.e_j1) return 0;
-  b.a_i0 = max(0, b.e_i0 - R);
-  b.a_j0 = max(0, b.e_j0 - R);
-  b.a_i1 = min(size_x, b.e_i1 + R);
-  b.a_j1 = min(size_y, b.e_j1 + R);
+  if (!infl_box(size_x, size_y, min_i, min_j, max_i, max_j, R, &b)) return 0;
   const int aw = b.a_i1 - b.a_i0, ah = b.a_j1 - b.a_j0, rows = b.e_j1 - b.e_j0;
 
   // cost by squared cell distance: cached_costs_[dx][dy] = computeCost(hypot(dx, dy)) (:313, :336)
@@ -208,7 +195,17 @@ int amclb200_inflate_costs(unsigned char *costs, int on_device, int size_x, int 
   const int words = (aw + 63) / 64;
   const int pad = (R + 1 + 63) / 64 + 1;
   grow(s.d_bits, s.bits_cap, (size_t)rows * (words + 2 * pad));
-  grow(s.d_g, s.g_cap, (size_t)rows * aw);
+  // AMCLB200_EDT=search keeps the per-cell search kernels for any radius (A/B timing)
+  static const bool force_search = [] {
+    const char *e = getenv("AMCLB200_EDT");
+    return e && strcmp(e, "search") == 0;
+  }();
+  const bool fast = R <= kFastRadius && !force_search;
+  const int g2_pitch = (aw + 7) & ~7;
+  if (fast)
+    grow(s.d_g2, s.g2_cap, (size_t)rows * g2_pitch);
+  else
+    grow(s.d_g, s.g_cap, (size_t)rows * aw);
   grow(s.d_lut, s.lut_cap, (size_t)R2 + 1);
   AMCL_CUDA(cudaMemcpyAsync(s.d_lut, lut.data(), (size_t)R2 + 1, cudaMemcpyHostToDevice, st));
 
@@ -240,11 +237,27 @@ int amclb200_inflate_costs(unsigned char *costs, int on_device, int size_x, int 
     AMCL_LAUNCH_CHECK();
   }
   if (rows > 65535 || ah > 65535) AMCL_FATAL("update windows taller than 65535 rows are not supported");
-  infl_row_dist<<<dim3((aw + 255) / 256, rows), 256, 0, st>>>(s.d_bits, aw, words, pad, R, s.d_g);
-  AMCL_LAUNCH_CHECK();
-  infl_col_apply<<<dim3((aw + 255) / 256, ah), 256, 0, st>>>(s.d_g, aw, k, R, s.d_lut, inflate_unknown,
-                                                             pitch, d_master);
-  AMCL_LAUNCH_CHECK();
+  if (fast)
+  {
+    edt_row_squares<<<dim3((g2_pitch / 8 + 255) / 256, rows), 256, 0, st>>>(s.d_bits, g2_pitch, words, pad, R,
+                                                                           s.d_g2);
+    AMCL_LAUNCH_CHECK();
+    const int chunks = (2 * R + 8 + 7) / 8;
+    const size_t smem = (size_t)(kColY - kColV + chunks * 8) * kColX * sizeof(uint16_t);
+    if (smem > 48 * 1024)
+      AMCL_CUDA(cudaFuncSetAttribute(infl_col_squares, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    infl_col_squares<<<dim3((aw + kColX - 1) / kColX, (ah + kColY - 1) / kColY), 256, smem, st>>>(
+        s.d_g2, g2_pitch, k, R, chunks, s.d_lut, inflate_unknown, pitch, d_master);
+    AMCL_LAUNCH_CHECK();
+  }
+  else
+  {
+    infl_row_dist<<<dim3((aw + 255) / 256, rows), 256, 0, st>>>(s.d_bits, aw, words, pad, R, s.d_g);
+    AMCL_LAUNCH_CHECK();
+    infl_col_apply<<<dim3((aw + 255) / 256, ah), 256, 0, st>>>(s.d_g, aw, k, R, s.d_lut, inflate_unknown,
+                                                               pitch, d_master);
+    AMCL_LAUNCH_CHECK();
+  }
   AMCL_CUDA(cudaEventRecord(ev1, st));
   if (!on_device)
     AMCL_CUDA(cudaMemcpy2DAsync(costs + (size_t)b.a_j0 * size_x + b.a_i0, (size_t)size_x, s.d_rows, (size_t)aw,

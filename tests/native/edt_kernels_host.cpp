@@ -54,3 +54,37 @@ extern "C" int edt_kernels_host(const int8_t *occ, int sx, int sy, int R, int us
   });
   return 0;
 }
+
+// ---- costmap inflation: edt_row_squares + infl_col_squares (inflation_kernels.cuh) ----
+#include "inflation_kernels.cuh"
+
+// costs: size_x * size_y cost values, updated in place as amclb200_inflate_costs
+// does on a device-resident grid.  cost_of_d2: R * R + 1 entries.  The lethal cells
+// of the seed window are packed on the host (infl_pack_rows does it on the device).
+extern "C" int infl_kernels_host(unsigned char *costs, int size_x, int size_y, int min_i, int min_j, int max_i,
+                                 int max_j, int R, const unsigned char *cost_of_d2, int inflate_unknown)
+{
+  if (R < 1 || R > kFastRadius) return -1;
+  InflBox b;
+  if (!infl_box(size_x, size_y, min_i, min_j, max_i, max_j, R, &b)) return 0;
+  const int aw = b.a_i1 - b.a_i0, ah = b.a_j1 - b.a_j0, rows = b.e_j1 - b.e_j0;
+  const int words = (aw + 63) / 64, pad = (R + 1 + 63) / 64 + 1, stride = words + 2 * pad;
+  std::vector<unsigned long long> bits((size_t)rows * stride, 0ull);
+  for (int r = 0; r < rows; r++)
+    for (int c = 0; c < aw; c++)
+    {
+      const int i = b.a_i0 + c;
+      if (i >= b.e_i0 && i < b.e_i1 && costs[(size_t)(b.e_j0 + r) * size_x + i] == COST_LETHAL)
+        bits[(size_t)r * stride + pad + (c >> 6)] |= 1ull << (c & 63);
+    }
+  const int pitch = (aw + 7) & ~7;
+  std::vector<uint16_t> g2((size_t)rows * pitch, 0xabcd);
+  launch(dim3((pitch / 8 + 255) / 256, rows), dim3(256),
+         [&] { edt_row_squares(bits.data(), pitch, words, pad, R, g2.data()); });
+  const int chunks = (2 * R + 8 + 7) / 8;
+  if ((size_t)(kColY - kColV + chunks * 8) * kColX * sizeof(uint16_t) > sizeof(s_raw)) return -2;
+  launch(dim3((aw + kColX - 1) / kColX, (ah + kColY - 1) / kColY), dim3(256), [&] {
+    infl_col_squares(g2.data(), pitch, b, R, chunks, cost_of_d2, inflate_unknown, size_x, costs);
+  });
+  return aw * ah;
+}

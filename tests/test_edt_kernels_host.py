@@ -88,3 +88,50 @@ def test_radius_above_the_fast_limit_is_refused(host_kernels):
     limit = host_kernels.edt_kernels_host_max_radius()
     assert limit == 160
     assert host_kernels.edt_kernels_host(occ.ctypes.data, 16, 8, limit + 1, 1, code.ctypes.data) == -1
+
+
+# ------------------------------------------------------- costmap inflation ----
+
+def host_inflate(lib, grid, window, resolution, inscribed, radius, weight, inflate_unknown):
+    """amclb200_inflate_costs's arithmetic around the kernels (inflation_dev.cu): cell
+    radius (costmap_2d.cpp:181-185) and cost by squared cell distance
+    (inflation_layer.h:104-119 through the oracle's orc_inflation_cost)."""
+    g = np.array(grid, dtype=np.uint8, order="C", copy=True)
+    sy, sx = g.shape
+    w = (0, 0, sx, sy) if window is None else window
+    R = int(max(0.0, np.ceil(radius / resolution)))
+    lut = np.zeros(R * R + 1, np.uint8)
+    for dx in range(R + 1):
+        for dy in range(dx, R + 1):
+            if dx * dx + dy * dy <= R * R:
+                lut[dx * dx + dy * dy] = oracle.port().orc_inflation_cost(float(np.hypot(dx, dy)), resolution,
+                                                                         inscribed, weight)
+    lib.infl_kernels_host.argtypes = [C.c_void_p] + [C.c_int] * 7 + [C.c_void_p, C.c_int]
+    rc = lib.infl_kernels_host(g.ctypes.data, sx, sy, w[0], w[1], w[2], w[3], R, lut.ctypes.data, int(inflate_unknown))
+    assert rc >= 0, rc
+    return g
+
+
+@pytest.mark.parametrize("seed,inflate_unknown", [(0, False), (1, True)])
+def test_inflation_kernels_on_host_vs_oracle(host_kernels, seed, inflate_unknown):
+    """The cases of tests/test_gpu_inflation.py::test_random_grids_and_windows on a
+    smaller grid: whole map, interior windows, windows at the corners, a one-cell
+    and an empty window."""
+    rng = np.random.default_rng(seed)
+    g = rng.choice(np.array([0, 0, 0, 0, 0, 0, 60, 128, 252, 253, 255], dtype=np.uint8), size=(150, 203))
+    g[rng.random(g.shape) < 0.01] = 254
+    for window in (None, (30, 20, 80, 60), (0, 0, 5, 5), (195, 140, 203, 150), (100, 70, 101, 71), (50, 50, 50, 50)):
+        got = host_inflate(host_kernels, g, window, 0.05, 0.12, 0.55, 10.0, inflate_unknown)
+        want = oracle.inflate(g, window, 0.05, 0.12, 0.55, 10.0, inflate_unknown, exact=True)
+        assert np.array_equal(got, want), window
+
+
+def test_inflation_kernels_on_host_large_radius(host_kernels):
+    g = np.zeros((90, 140), np.uint8)
+    g[40, 60] = 254
+    g[5, 130] = 254
+    g[80:, :10] = 255
+    for unknown in (False, True):
+        got = host_inflate(host_kernels, g, (20, 10, 120, 70), 0.05, 0.3, 3.0, 3.0, unknown)     # 60 cells
+        want = oracle.inflate(g, (20, 10, 120, 70), 0.05, 0.3, 3.0, 3.0, unknown, exact=True)
+        assert np.array_equal(got, want)

@@ -135,3 +135,13 @@ def test_full_size_properties(gpu_lib):
         assert np.all(patch[np.hypot(yy, xx) * 0.05 <= 0.2] >= INSCRIBED)
     sub = oracle.inflate(g[:300, :300], None, 0.05, 0.2, 0.55, 10.0, exact=True)
     assert np.array_equal(once[:280, :280], sub[:280, :280])
+
+
+def test_radius_above_the_register_block_limit(gpu_lib):
+    """200 cells > kFastRadius (160): the per-cell search kernels (infl_row_dist, infl_col_apply)."""
+    g = np.zeros((260, 300), dtype=np.uint8)
+    g[130, 150] = LETHAL
+    g[10, 290] = LETHAL
+    got = gpu_inflate(gpu_lib, g, (100, 100, 200, 160), 0.01, 0.05, 2.0, 3.0)
+    want = oracle.inflate(g, (100, 100, 200, 160), 0.01, 0.05, 2.0, 3.0, exact=True)
+    assert np.array_equal(got, want)
