@@ -140,18 +140,22 @@ def inflation_case(size):
 
 
 def main():
+    # `python profiles/run_configs.py maps` runs the map-side cases only (K3, N3)
+    only_maps = len(sys.argv) > 1 and sys.argv[1] == "maps"
     res = []
     res.append(inflation_case(4000))
-    res.append(sensor_case("K1 likelihood_field 5000 x 180, 1000^2", 1000, 5000, 180, "lf", resample=True))
-    res.append(sensor_case("K2 beam 100k x 360, 2000^2", 2000, 100000, 360, "beam"))
+    if not only_maps:
+        res.append(sensor_case("K1 likelihood_field 5000 x 180, 1000^2", 1000, 5000, 180, "lf", resample=True))
+        res.append(sensor_case("K2 beam 100k x 360, 2000^2", 2000, 100000, 360, "beam"))
     res.append(edt_case(2000))
     res.append(edt_case(4000))
-    for n in (1 << 20, 1 << 22, 1 << 24):
-        res.append(sensor_case("K4 likelihood_field_prob + resample, %d x 1080, 4000^2" % n, 4000, n, 1080,
-                               "lfp", resample=True))
-    res.append(sensor_case("K4t tracking cloud lfp + resample 4M x 1080", 4000, 1 << 22, 1080, "lfp",
-                           cloud_kind="tracking", resample=True))
-    out = os.path.join(ROOT, "gpurun_out", "configs_r2.json")
+    if not only_maps:
+        for n in (1 << 20, 1 << 22, 1 << 24):
+            res.append(sensor_case("K4 likelihood_field_prob + resample, %d x 1080, 4000^2" % n, 4000, n, 1080,
+                                   "lfp", resample=True))
+        res.append(sensor_case("K4t tracking cloud lfp + resample 4M x 1080", 4000, 1 << 22, 1080, "lfp",
+                               cloud_kind="tracking", resample=True))
+    out = os.path.join(ROOT, "gpurun_out", "configs_r2_maps.json" if only_maps else "configs_r2.json")
     os.makedirs(os.path.dirname(out), exist_ok=True)
     json.dump(res, open(out, "w"), indent=1)
     for r in res:
