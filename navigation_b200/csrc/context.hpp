@@ -90,6 +90,7 @@ struct MapCtx
   size_t lf_cap = 0;              // elements allocated
   int lf_apron = 0;               // cells on every side, a multiple of 4
   int lf_w = 0, lf_h = 0;         // cells including the apron, multiples of 4
+  cudaTextureObject_t lf_tex = 0; // d_lf as a linear texture of uint16 (0: not created)
   uint64_t lf_generation = 0;     // generation of d_code it was derived from (0: never)
   uint16_t *d_rank_of_code = nullptr;
   int rank_cap = 0;

@@ -184,6 +184,7 @@ void map_ctx_release(map_t *map)
   if (m->h_occ_pin) cudaFreeHost(m->h_occ_pin);
   if (m->h_code_pin) cudaFreeHost(m->h_code_pin);
   if (m->d_rowbits) cudaFree(m->d_rowbits);
+  if (m->lf_tex) cudaDestroyTextureObject(m->lf_tex);
   if (m->d_lf) cudaFree(m->d_lf);
   if (m->d_rank_of_code) cudaFree(m->d_rank_of_code);
   delete m;
@@ -548,9 +549,27 @@ void map_prepare_laser_view(MapCtx *m, int reach_cells)
   const size_t elems = (size_t)w * h;
   if (elems > m->lf_cap)
   {
+    if (m->lf_tex) cudaDestroyTextureObject(m->lf_tex);
+    m->lf_tex = 0;
     if (m->d_lf) cudaFree(m->d_lf);
     m->lf_cap = elems;
     AMCL_CUDA(cudaMalloc(&m->d_lf, elems * sizeof(uint16_t)));
+    // the same memory as a linear texture, for kernels that fetch through the texture pipe
+    int max_linear = 0;
+    cudaDeviceGetAttribute(&max_linear, cudaDevAttrMaxTexture1DLinearWidth, globals().device);
+    if (elems <= (size_t)max_linear)
+    {
+      cudaResourceDesc res;
+      memset(&res, 0, sizeof(res));
+      res.resType = cudaResourceTypeLinear;
+      res.res.linear.devPtr = m->d_lf;
+      res.res.linear.desc = cudaCreateChannelDesc<unsigned short>();
+      res.res.linear.sizeInBytes = elems * sizeof(uint16_t);
+      cudaTextureDesc td;
+      memset(&td, 0, sizeof(td));
+      td.readMode = cudaReadModeElementType;
+      AMCL_CUDA(cudaCreateTextureObject(&m->lf_tex, &res, &td, nullptr));
+    }
   }
   const long long tiles = (long long)(w >> 2) * (h >> 2);
   build_laser_view<<<(unsigned)((tiles + 255) / 256), 256, 0, globals().stream>>>(

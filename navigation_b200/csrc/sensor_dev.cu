@@ -88,6 +88,7 @@ struct LfArgs
   const unsigned char *agree;  // rank -> z < beam_skip_distance (COUNT mode)
   int nranks_pad;           // even
   const uint16_t *lf;       // laser view of the distance map (MapCtx::d_lf)
+  cudaTextureObject_t lf_tex;  // the same array as a linear texture (TEXQ > 0 only)
   unsigned max_i, max_j;    // lf_w - 1, lf_h - 1: both lie in the apron
   unsigned k_row;           // lf_w - 1 (see lf_index)
   double lx, ly, la;        // laser pose in the robot frame
@@ -143,7 +144,7 @@ __device__ __forceinline__ unsigned lf_index(unsigned mi, unsigned mj, unsigned 
 // l & (2^LOGC - 1) reads its own copy.  With 16 copies the 8-byte reads of a
 // half-warp never meet in a bank (ncu on the single-copy table: 4.4 wavefronts
 // per read, the largest share of the LSU pipe that bounds this kernel).
-template <int MODE, int LOGC, bool CLAMP>
+template <int MODE, int LOGC, bool CLAMP, int TEXQ>
 __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_beams,
                                              const double *lut_lane, const unsigned char *s_agree,
                                              int *s_count_row, int lane, int live,
@@ -166,7 +167,12 @@ __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_b
         mi = min(mi, max_i);
         mj = min(mj, max_j);
       }
-      r[q] = __ldg(lf + lf_index(mi, mj, k_row));
+      // the first TEXQ of the kBlockP gathers are texture fetches (TLD: the index is
+      // the operand, no 64-bit address is formed), the rest global loads
+      if (q < TEXQ)
+        r[q] = tex1Dfetch<unsigned short>(a.lf_tex, (int)lf_index(mi, mj, k_row));
+      else
+        r[q] = __ldg(lf + lf_index(mi, mj, k_row));
     }
   };
   auto consume = [&](int i, const unsigned (&r)[kBlockP]) {
@@ -192,7 +198,7 @@ __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_b
   }
 }
 
-template <int MODE, int LOGC>
+template <int MODE, int LOGC, int TEXQ = 0>
 __global__ void __launch_bounds__(kLfThreads, AMCL_LF_MINBLOCKS)
 likelihood_field_kernel(const LfArgs a)
 {
@@ -277,9 +283,9 @@ likelihood_field_kernel(const LfArgs a)
     }
     const int live = min(kBlockP, a.n - p0);
     if (all_inside)
-      lf_beam_loop<MODE, LOGC, false>(a, s_beams, lut_lane, s_agree, s_count_row, lane, live, pX, pY, pc, ps, acc);
+      lf_beam_loop<MODE, LOGC, false, TEXQ>(a, s_beams, lut_lane, s_agree, s_count_row, lane, live, pX, pY, pc, ps, acc);
     else
-      lf_beam_loop<MODE, LOGC, true>(a, s_beams, lut_lane, s_agree, s_count_row, lane, live, pX, pY, pc, ps, acc);
+      lf_beam_loop<MODE, LOGC, true, TEXQ>(a, s_beams, lut_lane, s_agree, s_count_row, lane, live, pX, pY, pc, ps, acc);
 
     // Every lane receives the kBlockP totals; lane q (< kBlockP) finishes
     // particle p0 + q, the one it loaded above, so that the exp() of the LFP
@@ -767,6 +773,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   a.agree = d_agree;
   a.nranks_pad = nranks_pad;
   a.lf = m->d_lf;
+  a.lf_tex = m->lf_tex;
   a.max_i = (unsigned)m->lf_w - 1u;
   a.max_j = (unsigned)m->lf_h - 1u;
   a.k_row = (unsigned)m->lf_w - 1u;
@@ -798,23 +805,35 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
     AMCL_CUDA(cudaEventCreate(&c->ev_b));
   }
   AMCL_CUDA(cudaEventRecord(c->ev_a, st));
-#define AMCL_LF_LAUNCH(MODE, LOGC)                                                       \
+  // How many of the kBlockP gathers per lane go through the texture pipe.  Measured
+  // at 16 Mi x 1059 (profiles/r2_lf_kernel.md): likelihood_field 15.52 ms with loads,
+  // 14.66 ms with fetches; likelihood_field_prob 15.10 / 15.47 -- the loops are the
+  // same source, the difference is ptxas's schedule, so each model ships the faster.
+  // AMCLB200_LF_TEXQ=0|8 overrides (A/B timing).
+  static const int texq_env = [] {
+    const char *e = getenv("AMCLB200_LF_TEXQ");
+    return e ? atoi(e) : -1;
+  }();
+  int texq = texq_env >= 0 ? texq_env : (model == 1 ? kBlockP : 0);
+  if (!m->lf_tex || logc != 4 || count_mode) texq = 0;
+#define AMCL_LF_LAUNCH(MODE, LOGC, TEXQ)                                                 \
   do                                                                                     \
   {                                                                                      \
-    grid = persistent_grid(likelihood_field_kernel<MODE, LOGC>, kLfThreads, smem);       \
+    grid = persistent_grid(likelihood_field_kernel<MODE, LOGC, TEXQ>, kLfThreads, smem); \
     int need_blocks = (n + (kLfThreads / 32) * kBlockP - 1) / ((kLfThreads / 32) * kBlockP); \
     if (grid > need_blocks) grid = need_blocks > 0 ? need_blocks : 1;                    \
     ensure_partials(c, grid);                                                            \
     a.block_totals = c->d_partials;                                                      \
-    likelihood_field_kernel<MODE, LOGC><<<grid, kLfThreads, smem, st>>>(a);              \
+    likelihood_field_kernel<MODE, LOGC, TEXQ><<<grid, kLfThreads, smem, st>>>(a);        \
   } while (0)
 #define AMCL_LF_DISPATCH(MODE)                       \
   do                                                 \
   {                                                  \
-    if (logc == 4) AMCL_LF_LAUNCH(MODE, 4);          \
-    else if (logc == 2) AMCL_LF_LAUNCH(MODE, 2);     \
-    else if (logc == 0) AMCL_LF_LAUNCH(MODE, 0);     \
-    else AMCL_LF_LAUNCH(MODE, -1);                   \
+    if (logc == 4 && texq == kBlockP) AMCL_LF_LAUNCH(MODE, 4, kBlockP); \
+    else if (logc == 4) AMCL_LF_LAUNCH(MODE, 4, 0);  \
+    else if (logc == 2) AMCL_LF_LAUNCH(MODE, 2, 0);  \
+    else if (logc == 0) AMCL_LF_LAUNCH(MODE, 0, 0);  \
+    else AMCL_LF_LAUNCH(MODE, -1, 0);                \
   } while (0)
 
   if (count_mode) AMCL_LF_DISPATCH(MODE_COUNT);
