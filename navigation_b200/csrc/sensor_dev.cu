@@ -122,6 +122,13 @@ constexpr double kCellGuard = 536870912.0;  // 2^29: beyond this nothing is on a
 #define AMCL_LF_BLOCKP 8
 #endif
 constexpr int kBlockP = AMCL_LF_BLOCKP;
+#ifndef AMCL_LF_LOAD
+#define AMCL_LF_LOAD 0
+#endif
+#ifndef AMCL_LF_UNROLL
+#define AMCL_LF_UNROLL 3
+#endif
+constexpr int kLfUnroll = AMCL_LF_UNROLL;   // beams per lane in flight on the texture path
 
 // Offset of cell (mi, mj) in the laser view: 4x4 tiles, tiles row-major, cells
 // of a tile column-first,
@@ -155,8 +162,24 @@ __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_b
   const uint16_t *__restrict__ lf = a.lf;
   const unsigned k_row = a.k_row, max_i = a.max_i, max_j = a.max_j;
   constexpr int kShift = LOGC < 0 ? 0 : LOGC;
+  auto load_cell = [&](int q, unsigned idx) -> unsigned {
+    // the first TEXQ of the kBlockP gathers are texture fetches (TLD: the index is
+    // the operand, no 64-bit address is formed), the rest global loads
+    if (q < TEXQ) return tex1Dfetch<unsigned short>(a.lf_tex, (int)idx);
+#if AMCL_LF_LOAD == 1      /* kernel-variant experiments only: L2 only */
+    return __ldcg(lf + idx);
+#elif AMCL_LF_LOAD == 2    /* ... read-only path, no L1 allocation */
+    unsigned short v;
+    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(v) : "l"(lf + idx));
+    return v;
+#else
+    return __ldg(lf + idx);
+#endif
+  };
   auto gather = [&](int i, unsigned (&r)[kBlockP]) {
     const double2 b = s_beams[i];
+#ifdef AMCL_LF_TWO_PHASE   /* kernel-variant experiments only: all offsets first, then the loads */
+    unsigned idx[kBlockP];
 #pragma unroll
     for (int q = 0; q < kBlockP; q++)
     {
@@ -167,13 +190,24 @@ __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_b
         mi = min(mi, max_i);
         mj = min(mj, max_j);
       }
-      // the first TEXQ of the kBlockP gathers are texture fetches (TLD: the index is
-      // the operand, no 64-bit address is formed), the rest global loads
-      if (q < TEXQ)
-        r[q] = tex1Dfetch<unsigned short>(a.lf_tex, (int)lf_index(mi, mj, k_row));
-      else
-        r[q] = __ldg(lf + lf_index(mi, mj, k_row));
+      idx[q] = lf_index(mi, mj, k_row);
     }
+#pragma unroll
+    for (int q = 0; q < kBlockP; q++) r[q] = load_cell(q, idx[q]);
+#else
+#pragma unroll
+    for (int q = 0; q < kBlockP; q++)
+    {
+      unsigned mi = (unsigned)floor_to_int(fma(pc[q], b.x, fma(-ps[q], b.y, pX[q])));
+      unsigned mj = (unsigned)floor_to_int(fma(ps[q], b.x, fma(pc[q], b.y, pY[q])));
+      if (CLAMP)
+      {
+        mi = min(mi, max_i);
+        mj = min(mj, max_j);
+      }
+      r[q] = load_cell(q, lf_index(mi, mj, k_row));
+    }
+#endif
   };
   auto consume = [&](int i, const unsigned (&r)[kBlockP]) {
     if (MODE == MODE_COUNT)
@@ -190,6 +224,10 @@ __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_b
   // (Issuing the gathers of beam i + 32 before the table reads of beam i was
   // measured twice and loses: the L1TEX pipe, not the gather latency, is what
   // this loop waits for -- profiles/r2_lf_kernel.md.)
+  // With texture fetches, three beams per lane are in flight together (24 fetches
+  // per lane, 384 per SM sub-partition's 4 warps): 14.66 -> 13.25 ms at 16 Mi x 1059;
+  // two 13.97, four 13.82 (spills).  With loads, unrolling gains nothing (15.15).
+#pragma unroll (TEXQ > 0 ? kLfUnroll : 1)
   for (int i = lane; i < a.nb; i += 32)
   {
     unsigned r[kBlockP];
@@ -805,16 +843,16 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
     AMCL_CUDA(cudaEventCreate(&c->ev_b));
   }
   AMCL_CUDA(cudaEventRecord(c->ev_a, st));
-  // How many of the kBlockP gathers per lane go through the texture pipe.  Measured
+  // The map gathers are texture fetches with three beams per lane in flight.  Measured
   // at 16 Mi x 1059 (profiles/r2_lf_kernel.md): likelihood_field 15.52 ms with loads,
-  // 14.66 ms with fetches; likelihood_field_prob 15.10 / 15.47 -- the loops are the
-  // same source, the difference is ptxas's schedule, so each model ships the faster.
+  // 13.25 ms with fetches; likelihood_field_prob 15.10 / 14.05.  The counting pass of
+  // beam skipping and maps too large for a linear texture keep the loads.
   // AMCLB200_LF_TEXQ=0|8 overrides (A/B timing).
   static const int texq_env = [] {
     const char *e = getenv("AMCLB200_LF_TEXQ");
     return e ? atoi(e) : -1;
   }();
-  int texq = texq_env >= 0 ? texq_env : (model == 1 ? kBlockP : 0);
+  int texq = texq_env >= 0 ? texq_env : kBlockP;
   if (!m->lf_tex || logc != 4 || count_mode) texq = 0;
 #define AMCL_LF_LAUNCH(MODE, LOGC, TEXQ)                                                 \
   do                                                                                     \
