@@ -315,7 +315,8 @@ def rooflines(lib, args, k_ms, n_local, used_beams, ms_step, st_action, st_resam
         "peak_source": "measured live: uncorrelated 2-byte gathers, one 32-B sector each, over a %.1f MB table "
                        "(= %.2f sectors per clock per SM: the probe is bound by the L1TEX sector rate, not by "
                        "its index arithmetic)" % (map_bytes / 1e6, gather_rate / (148 * 1.965e9)),
-        "ncu_recorded": ({k: rec[k] for k in ("commit", "l1tex_sectors", "l1tex_lsu_pipe_pct", "issue_active_pct",
+        "ncu_recorded": ({k: rec[k] for k in ("commit", "l1tex_sectors", "l1tex_sectors_texture", "l1tex_lsu_pipe_pct",
+                                             "l1tex_tex_pipe_pct", "issue_active_pct",
                                              "fp64_pipe_pct", "l2_hit_pct", "kernel_ms_under_ncu") if k in rec}
                          if rec else "no recorded capture for %d particles per launch" % n_local),
         "ncu_scaled_from": (None if scaled_from is None else

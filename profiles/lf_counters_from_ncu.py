@@ -32,7 +32,11 @@ def main():
         "kernel": d.get("Kernel Name", "likelihood_field_kernel"),
         "kernel_ms_under_ncu": num("gpu__time_duration.sum") * {"ms": 1, "us": 1e-3, "s": 1e3, "ns": 1e-6}[u["gpu__time_duration.sum"]],
         "l2_sectors_read": int(num("lts__t_sectors_srcunit_tex_op_read.sum")),
-        "l1tex_sectors": int(num("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum")),
+        # map cells arrive as global loads (round-2 kernel up to 3b66385) or texture fetches (after)
+        "l1tex_sectors": int(num("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum")
+                             + num("l1tex__t_sectors_pipe_tex_mem_texture.sum")),
+        "l1tex_sectors_texture": int(num("l1tex__t_sectors_pipe_tex_mem_texture.sum")),
+        "l1tex_tex_pipe_pct": num("l1tex__data_pipe_tex_wavefronts.avg.pct_of_peak_sustained_elapsed"),
         "dram_bytes": int(nbytes("dram__bytes_read.sum") + nbytes("dram__bytes_write.sum")),
         "l1tex_lsu_pipe_pct": num("l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed"),
         "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
