@@ -864,9 +864,20 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
     a.block_totals = c->d_partials;                                                      \
     likelihood_field_kernel<MODE, LOGC, TEXQ><<<grid, kLfThreads, smem, st>>>(a);        \
   } while (0)
+#ifdef AMCL_LF_TEXQ_EXPERIMENT   /* kernel-variant experiments only: fetches for some particles, loads for the rest */
+#define AMCL_LF_TEXQ_SPLITS(MODE)                                       \
+    if (logc == 4 && texq == 4) AMCL_LF_LAUNCH(MODE, 4, 4);             \
+    else if (logc == 4 && texq == 5) AMCL_LF_LAUNCH(MODE, 4, 5);        \
+    else if (logc == 4 && texq == 6) AMCL_LF_LAUNCH(MODE, 4, 6);        \
+    else if (logc == 4 && texq == 7) AMCL_LF_LAUNCH(MODE, 4, 7);        \
+    else
+#else
+#define AMCL_LF_TEXQ_SPLITS(MODE)
+#endif
 #define AMCL_LF_DISPATCH(MODE)                       \
   do                                                 \
   {                                                  \
+    AMCL_LF_TEXQ_SPLITS(MODE)                                            \
     if (logc == 4 && texq == kBlockP) AMCL_LF_LAUNCH(MODE, 4, kBlockP); \
     else if (logc == 4) AMCL_LF_LAUNCH(MODE, 4, 0);  \
     else if (logc == 2) AMCL_LF_LAUNCH(MODE, 2, 0);  \
@@ -879,6 +890,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   else AMCL_LF_DISPATCH(MODE_LFP);
 #undef AMCL_LF_DISPATCH
 #undef AMCL_LF_LAUNCH
+#undef AMCL_LF_TEXQ_SPLITS
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaEventRecord(c->ev_b, st));
 
