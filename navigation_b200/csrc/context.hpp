@@ -91,6 +91,10 @@ struct MapCtx
   int lf_apron = 0;               // cells on every side, a multiple of 4
   int lf_w = 0, lf_h = 0;         // cells including the apron, multiples of 4
   cudaTextureObject_t lf_tex = 0; // d_lf as a linear texture of uint16 (0: not created)
+  cudaArray_t lf_array = nullptr; // the laser view row by row in a 2-D array (texture-unit layout)
+  cudaTextureObject_t lf_tex2d = 0;
+  cudaSurfaceObject_t lf_surf = 0;
+  int lf_array_w = 0, lf_array_h = 0;
   uint64_t lf_generation = 0;     // generation of d_code it was derived from (0: never)
   uint16_t *d_rank_of_code = nullptr;
   int rank_cap = 0;

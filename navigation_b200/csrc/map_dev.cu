@@ -186,6 +186,9 @@ void map_ctx_release(map_t *map)
   if (m->d_rowbits) cudaFree(m->d_rowbits);
   if (m->lf_tex) cudaDestroyTextureObject(m->lf_tex);
   if (m->d_lf) cudaFree(m->d_lf);
+  if (m->lf_tex2d) cudaDestroyTextureObject(m->lf_tex2d);
+  if (m->lf_surf) cudaDestroySurfaceObject(m->lf_surf);
+  if (m->lf_array) cudaFreeArray(m->lf_array);
   if (m->d_rank_of_code) cudaFree(m->d_rank_of_code);
   delete m;
   r.erase(it);
@@ -537,6 +540,48 @@ __global__ void build_laser_view(const uint16_t *__restrict__ code, int tiles_x,
 // that wide when memory allows (at most the map's own size again plus 64 MB), so
 // that every particle on the map takes the clamp-free path; a narrower apron only
 // sends the particles near the border through the clamped path.
+// The same ranks into a 2-D array through a surface: one thread per 4x4 tile of the
+// view, four 8-byte stores.
+__global__ void build_laser_array(const uint16_t *__restrict__ code, int tiles_x, int sx, int sy,
+                                  const uint16_t *__restrict__ rank_of_code, int off_rank,
+                                  int apron, int w, int h, cudaSurfaceObject_t surf)
+{
+  const int tw = w >> 2;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)tw * (h >> 2)) return;
+  const int ti = (int)(t % tw), tj = (int)(t / tw);
+  const int si = ti - (apron >> 2), sj = tj - (apron >> 2);
+  const bool on_map = si >= 0 && sj >= 0 && si * 4 < sx && sj * 4 < sy;
+  __align__(16) uint16_t c[16];
+  if (on_map)
+  {
+    const uint4 *src = reinterpret_cast<const uint4 *>(code + ((size_t)sj * tiles_x + si) * 16);
+    *reinterpret_cast<uint4 *>(c) = __ldg(src);
+    *reinterpret_cast<uint4 *>(c + 8) = __ldg(src + 1);
+  }
+#pragma unroll
+  for (int lj = 0; lj < 4; lj++)
+  {
+    ushort4 v;
+    v.x = on_map ? __ldg(rank_of_code + c[lj * 4 + 0]) : (uint16_t)off_rank;
+    v.y = on_map ? __ldg(rank_of_code + c[lj * 4 + 1]) : (uint16_t)off_rank;
+    v.z = on_map ? __ldg(rank_of_code + c[lj * 4 + 2]) : (uint16_t)off_rank;
+    v.w = on_map ? __ldg(rank_of_code + c[lj * 4 + 3]) : (uint16_t)off_rank;
+    surf2Dwrite(v, surf, ti * 4 * (int)sizeof(uint16_t), tj * 4 + lj);
+  }
+}
+
+static void release_laser_array(MapCtx *m)
+{
+  if (m->lf_tex2d) cudaDestroyTextureObject(m->lf_tex2d);
+  if (m->lf_surf) cudaDestroySurfaceObject(m->lf_surf);
+  if (m->lf_array) cudaFreeArray(m->lf_array);
+  m->lf_tex2d = 0;
+  m->lf_surf = 0;
+  m->lf_array = nullptr;
+  m->lf_array_w = m->lf_array_h = 0;
+}
+
 void map_prepare_laser_view(MapCtx *m, int reach_cells)
 {
   if (!m->dist_valid) AMCL_FATAL("laser view requested before map_update_cspace()");
@@ -576,6 +621,50 @@ void map_prepare_laser_view(MapCtx *m, int reach_cells)
       m->d_code, m->tiles_x, m->sx, m->sy, m->d_rank_of_code, (int)m->code_of_rank.size() - 1,
       apron, w, h, m->d_lf);
   AMCL_LAUNCH_CHECK();
+  // The view row by row in a 2-D array as well: the likelihood-field kernels fetch
+  // texels from it (the texture unit does the addressing).  AMCLB200_LF_TEX2D=0 leaves
+  // it out (A/B timing; the kernels then fetch from the linear texture).
+  static const bool want_array = [] {
+    const char *e = getenv("AMCLB200_LF_TEX2D");
+    return !e || atoi(e) != 0;
+  }();
+  if (want_array)
+  {
+    if (m->lf_array_w != w || m->lf_array_h != h)
+    {
+      release_laser_array(m);
+      const cudaChannelFormatDesc desc = cudaCreateChannelDesc<unsigned short>();
+      if (cudaMallocArray(&m->lf_array, &desc, (size_t)w, (size_t)h, cudaArraySurfaceLoadStore) == cudaSuccess)
+      {
+        cudaResourceDesc res;
+        memset(&res, 0, sizeof(res));
+        res.resType = cudaResourceTypeArray;
+        res.res.array.array = m->lf_array;
+        cudaTextureDesc td;
+        memset(&td, 0, sizeof(td));
+        td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModePoint;
+        td.readMode = cudaReadModeElementType;
+        td.normalizedCoords = 0;
+        AMCL_CUDA(cudaCreateTextureObject(&m->lf_tex2d, &res, &td, nullptr));
+        AMCL_CUDA(cudaCreateSurfaceObject(&m->lf_surf, &res));
+        m->lf_array_w = w;
+        m->lf_array_h = h;
+      }
+      else
+      {
+        cudaGetLastError();          // too large for an array: the linear view serves
+        m->lf_array = nullptr;
+      }
+    }
+    if (m->lf_array)
+    {
+      build_laser_array<<<(unsigned)((tiles + 255) / 256), 256, 0, globals().stream>>>(
+          m->d_code, m->tiles_x, m->sx, m->sy, m->d_rank_of_code, (int)m->code_of_rank.size() - 1,
+          apron, w, h, m->lf_surf);
+      AMCL_LAUNCH_CHECK();
+    }
+  }
   m->lf_apron = apron;
   m->lf_w = w;
   m->lf_h = h;

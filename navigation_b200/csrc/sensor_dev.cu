@@ -89,6 +89,7 @@ struct LfArgs
   int nranks_pad;           // even
   const uint16_t *lf;       // laser view of the distance map (MapCtx::d_lf)
   cudaTextureObject_t lf_tex;  // the same array as a linear texture (TEXQ > 0 only)
+  cudaTextureObject_t lf_tex2d;  // the laser view as a 2-D array texture, clamp addressing (TEXQ == kTex2D)
   unsigned max_i, max_j;    // lf_w - 1, lf_h - 1: both lie in the apron
   unsigned k_row;           // lf_w - 1 (see lf_index)
   double lx, ly, la;        // laser pose in the robot frame
@@ -128,7 +129,23 @@ constexpr int kBlockP = AMCL_LF_BLOCKP;
 #ifndef AMCL_LF_UNROLL
 #define AMCL_LF_UNROLL 3
 #endif
-constexpr int kLfUnroll = AMCL_LF_UNROLL;   // beams per lane in flight on the texture path
+constexpr int kLfUnroll = AMCL_LF_UNROLL;   // beams per lane in flight, linear texture
+#ifndef AMCL_LF_UNROLL_2D
+#define AMCL_LF_UNROLL_2D 2
+#endif
+constexpr int kLfUnroll2D = AMCL_LF_UNROLL_2D;   // ... 2-D array texture
+constexpr int kTex2D = 100;                 // TEXQ value: every gather is a 2-D texel fetch
+
+// Texel (x, y) of a 2-D uint16 texture, integer coordinates, which must lie inside
+// the array.
+__device__ __forceinline__ unsigned texel_2d(cudaTextureObject_t tex, int x, int y)
+{
+  unsigned r0, r1, r2, r3;
+  asm("tex.2d.v4.u32.s32 {%0, %1, %2, %3}, [%4, {%5, %6}];"
+      : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+      : "l"(tex), "r"(x), "r"(y));
+  return r0;
+}
 
 // Offset of cell (mi, mj) in the laser view: 4x4 tiles, tiles row-major, cells
 // of a tile column-first,
@@ -205,7 +222,12 @@ __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_b
         mi = min(mi, max_i);
         mj = min(mj, max_j);
       }
-      r[q] = load_cell(q, lf_index(mi, mj, k_row));
+      // 2-D array: the texture unit does the addressing (a texel fetch outside the
+      // array returns 0, not the edge, so the clamp above stays)
+      if (TEXQ == kTex2D)
+        r[q] = texel_2d(a.lf_tex2d, (int)mi, (int)mj);
+      else
+        r[q] = load_cell(q, lf_index(mi, mj, k_row));
     }
 #endif
   };
@@ -224,10 +246,11 @@ __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_b
   // (Issuing the gathers of beam i + 32 before the table reads of beam i was
   // measured twice and loses: the L1TEX pipe, not the gather latency, is what
   // this loop waits for -- profiles/r2_lf_kernel.md.)
-  // With texture fetches, three beams per lane are in flight together (24 fetches
-  // per lane, 384 per SM sub-partition's 4 warps): 14.66 -> 13.25 ms at 16 Mi x 1059;
-  // two 13.97, four 13.82 (spills).  With loads, unrolling gains nothing (15.15).
-#pragma unroll (TEXQ > 0 ? kLfUnroll : 1)
+  // With texel fetches several beams per lane are in flight together.  16 Mi x 1059,
+  // linear texture: one beam 14.66 ms, two 13.97, three 13.25, four 13.82 (spills);
+  // 2-D array: two 12.27, three 12.75, four 12.75, five 12.40.  With loads, unrolling
+  // gains nothing (15.15).
+#pragma unroll (TEXQ == kTex2D ? kLfUnroll2D : (TEXQ > 0 ? kLfUnroll : 1))
   for (int i = lane; i < a.nb; i += 32)
   {
     unsigned r[kBlockP];
@@ -812,6 +835,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   a.nranks_pad = nranks_pad;
   a.lf = m->d_lf;
   a.lf_tex = m->lf_tex;
+  a.lf_tex2d = m->lf_tex2d;
   a.max_i = (unsigned)m->lf_w - 1u;
   a.max_j = (unsigned)m->lf_h - 1u;
   a.k_row = (unsigned)m->lf_w - 1u;
@@ -843,17 +867,19 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
     AMCL_CUDA(cudaEventCreate(&c->ev_b));
   }
   AMCL_CUDA(cudaEventRecord(c->ev_a, st));
-  // The map gathers are texture fetches with three beams per lane in flight.  Measured
-  // at 16 Mi x 1059 (profiles/r2_lf_kernel.md): likelihood_field 15.52 ms with loads,
-  // 13.25 ms with fetches; likelihood_field_prob 15.10 / 14.05.  The counting pass of
-  // beam skipping and maps too large for a linear texture keep the loads.
-  // AMCLB200_LF_TEXQ=0|8 overrides (A/B timing).
+  // The map gathers are texel fetches with three beams per lane in flight.  Measured
+  // at 16 Mi x 1059 (profiles/r2_lf_kernel.md), likelihood_field / likelihood_field_prob:
+  // loads 15.52 / 15.10 ms, fetches from the linear texture 13.26 / 14.06 ms, fetches
+  // from the 2-D array 12.78 / 12.93 ms.  The counting pass of beam skipping keeps the
+  // loads; a view too large for an array falls back to the linear texture, then to loads.
+  // AMCLB200_LF_TEXQ=0|8|100 overrides (A/B timing).
   static const int texq_env = [] {
     const char *e = getenv("AMCLB200_LF_TEXQ");
     return e ? atoi(e) : -1;
   }();
-  int texq = texq_env >= 0 ? texq_env : kBlockP;
-  if (!m->lf_tex || logc != 4 || count_mode) texq = 0;
+  int texq = texq_env >= 0 ? texq_env : kTex2D;
+  if (texq == kTex2D && !m->lf_tex2d) texq = kBlockP;
+  if ((texq != kTex2D && !m->lf_tex) || logc != 4 || count_mode) texq = 0;
 #define AMCL_LF_LAUNCH(MODE, LOGC, TEXQ)                                                 \
   do                                                                                     \
   {                                                                                      \
@@ -878,7 +904,8 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   do                                                 \
   {                                                  \
     AMCL_LF_TEXQ_SPLITS(MODE)                                            \
-    if (logc == 4 && texq == kBlockP) AMCL_LF_LAUNCH(MODE, 4, kBlockP); \
+    if (logc == 4 && texq == kTex2D) AMCL_LF_LAUNCH(MODE, 4, kTex2D);   \
+    else if (logc == 4 && texq == kBlockP) AMCL_LF_LAUNCH(MODE, 4, kBlockP); \
     else if (logc == 4) AMCL_LF_LAUNCH(MODE, 4, 0);  \
     else if (logc == 2) AMCL_LF_LAUNCH(MODE, 2, 0);  \
     else if (logc == 0) AMCL_LF_LAUNCH(MODE, 0, 0);  \
