@@ -123,9 +123,6 @@ constexpr double kCellGuard = 536870912.0;  // 2^29: beyond this nothing is on a
 #define AMCL_LF_BLOCKP 8
 #endif
 constexpr int kBlockP = AMCL_LF_BLOCKP;
-#ifndef AMCL_LF_LOAD
-#define AMCL_LF_LOAD 0
-#endif
 #ifndef AMCL_LF_UNROLL
 #define AMCL_LF_UNROLL 3
 #endif
@@ -183,35 +180,10 @@ __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_b
     // the first TEXQ of the kBlockP gathers are texture fetches (TLD: the index is
     // the operand, no 64-bit address is formed), the rest global loads
     if (q < TEXQ) return tex1Dfetch<unsigned short>(a.lf_tex, (int)idx);
-#if AMCL_LF_LOAD == 1      /* kernel-variant experiments only: L2 only */
-    return __ldcg(lf + idx);
-#elif AMCL_LF_LOAD == 2    /* ... read-only path, no L1 allocation */
-    unsigned short v;
-    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(v) : "l"(lf + idx));
-    return v;
-#else
     return __ldg(lf + idx);
-#endif
   };
   auto gather = [&](int i, unsigned (&r)[kBlockP]) {
     const double2 b = s_beams[i];
-#ifdef AMCL_LF_TWO_PHASE   /* kernel-variant experiments only: all offsets first, then the loads */
-    unsigned idx[kBlockP];
-#pragma unroll
-    for (int q = 0; q < kBlockP; q++)
-    {
-      unsigned mi = (unsigned)floor_to_int(fma(pc[q], b.x, fma(-ps[q], b.y, pX[q])));
-      unsigned mj = (unsigned)floor_to_int(fma(ps[q], b.x, fma(pc[q], b.y, pY[q])));
-      if (CLAMP)
-      {
-        mi = min(mi, max_i);
-        mj = min(mj, max_j);
-      }
-      idx[q] = lf_index(mi, mj, k_row);
-    }
-#pragma unroll
-    for (int q = 0; q < kBlockP; q++) r[q] = load_cell(q, idx[q]);
-#else
 #pragma unroll
     for (int q = 0; q < kBlockP; q++)
     {
@@ -229,7 +201,6 @@ __device__ __forceinline__ void lf_beam_loop(const LfArgs &a, const double2 *s_b
       else
         r[q] = load_cell(q, lf_index(mi, mj, k_row));
     }
-#endif
   };
   auto consume = [&](int i, const unsigned (&r)[kBlockP]) {
     if (MODE == MODE_COUNT)
@@ -890,20 +861,9 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
     a.block_totals = c->d_partials;                                                      \
     likelihood_field_kernel<MODE, LOGC, TEXQ><<<grid, kLfThreads, smem, st>>>(a);        \
   } while (0)
-#ifdef AMCL_LF_TEXQ_EXPERIMENT   /* kernel-variant experiments only: fetches for some particles, loads for the rest */
-#define AMCL_LF_TEXQ_SPLITS(MODE)                                       \
-    if (logc == 4 && texq == 4) AMCL_LF_LAUNCH(MODE, 4, 4);             \
-    else if (logc == 4 && texq == 5) AMCL_LF_LAUNCH(MODE, 4, 5);        \
-    else if (logc == 4 && texq == 6) AMCL_LF_LAUNCH(MODE, 4, 6);        \
-    else if (logc == 4 && texq == 7) AMCL_LF_LAUNCH(MODE, 4, 7);        \
-    else
-#else
-#define AMCL_LF_TEXQ_SPLITS(MODE)
-#endif
 #define AMCL_LF_DISPATCH(MODE)                       \
   do                                                 \
   {                                                  \
-    AMCL_LF_TEXQ_SPLITS(MODE)                                            \
     if (logc == 4 && texq == kTex2D) AMCL_LF_LAUNCH(MODE, 4, kTex2D);   \
     else if (logc == 4 && texq == kBlockP) AMCL_LF_LAUNCH(MODE, 4, kBlockP); \
     else if (logc == 4) AMCL_LF_LAUNCH(MODE, 4, 0);  \
@@ -917,7 +877,7 @@ double run_likelihood_field(PfCtx *c, int which, MapCtx *m, int model,
   else AMCL_LF_DISPATCH(MODE_LFP);
 #undef AMCL_LF_DISPATCH
 #undef AMCL_LF_LAUNCH
-#undef AMCL_LF_TEXQ_SPLITS
+
   AMCL_LAUNCH_CHECK();
   AMCL_CUDA(cudaEventRecord(c->ev_b, st));
 
